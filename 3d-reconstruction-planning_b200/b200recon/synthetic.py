@@ -1,0 +1,59 @@
+"""Synthetic RGB-D sequences: camera orbits and scene constants.
+
+Replaces the reference's frame sources, which need a GL renderer or camera hardware
+("unavailable on this box"): bullet_camera.py:48-85 (PyBullet GL camera) and
+data_recorder.py:104-121 (RealSense D435).  The orbit mirrors main.py:68-136 (camera circling
+the object, looking at it).  Host-side float64 pose math only; pixels are produced by the CUDA
+ray caster (b2r_raycast_scene).
+"""
+import numpy as np
+
+# D435 colour intrinsics used everywhere in the reference (stitcher.py:264-267, main.py:241-244)
+D435_640x480 = dict(width=640, height=480, fx=615.6707153320312, fy=615.962158203125,
+                    cx=326.0557861328125, cy=240.55592346191406)
+# synthetic 720p mode for BASELINE config 5 (the reference has no 720p mode)
+SYN_1280x720 = dict(width=1280, height=720, fx=923.5, fy=923.5, cx=639.5, cy=359.5)
+
+# YCB 011_banana bounding box / 2 as an ellipsoid resting on the plane z = 0
+ELLIPSOID_R = (0.084, 0.034, 0.020)
+ELLIPSOID_C = (0.0, 0.0, 0.020)
+
+
+def look_at(eye, target, up=(0.0, 0.0, 1.0)):
+    """camera->world 4x4 for a pinhole camera at `eye` looking at `target`
+    (camera axes: +z forward, +x right, +y down, like Open3D / the D435)."""
+    eye = np.asarray(eye, np.float64)
+    target = np.asarray(target, np.float64)
+    f = target - eye
+    f /= np.linalg.norm(f)
+    upv = np.asarray(up, np.float64)
+    r = np.cross(f, upv)
+    if np.linalg.norm(r) < 1e-9:
+        r = np.cross(f, np.array([0.0, 1.0, 0.0]))
+    r /= np.linalg.norm(r)
+    d = np.cross(f, r)  # camera +y (down)
+    c2w = np.eye(4)
+    c2w[:3, 0], c2w[:3, 1], c2w[:3, 2], c2w[:3, 3] = r, d, f, eye
+    return c2w
+
+
+def orbit_poses(n_frames, radius=0.5, elevation_deg=30.0, target=(0.0, 0.0, 0.02), az0=0.0, az_span=2 * np.pi):
+    """n_frames camera->world poses on a circle of `radius` around `target`."""
+    el = np.deg2rad(elevation_deg)
+    out = []
+    for k in range(n_frames):
+        az = az0 + az_span * k / n_frames
+        eye = np.asarray(target, np.float64) + radius * np.array(
+            [np.cos(el) * np.cos(az), np.cos(el) * np.sin(az), np.sin(el)])
+        out.append(look_at(eye, target))
+    return out
+
+
+def extrinsic_from_pose(cam_to_world):
+    """Open3D extrinsic = world->camera."""
+    return np.linalg.inv(np.asarray(cam_to_world, np.float64))
+
+
+def volume_origin(length):
+    """cube of side L with the ground plane z=0 inside, object at the xy centre."""
+    return np.array([-0.5 * length, -0.5 * length, -0.1 * length])
