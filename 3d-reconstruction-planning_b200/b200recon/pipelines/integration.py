@@ -1,0 +1,219 @@
+"""`o3d.pipelines.integration`: UniformTSDFVolume on the B200 (north_star API).
+
+    vol = UniformTSDFVolume(length, resolution, sdf_trunc, color_type, origin)
+    vol.integrate(rgbd, intrinsic, extrinsic)
+    mesh = vol.extract_triangle_mesh();  pcd = vol.extract_point_cloud()
+
+Multi-GPU: pass `z_range=(z_begin, z_end)` to own one z-slab of the cube; `parallel.SlabVolume` wires
+the slabs of all ranks together (halo exchange + gather over NCCL).
+"""
+import ctypes as C
+import enum
+
+import numpy as np
+
+from .. import _lib, geometry, runtime
+
+
+class TSDFVolumeColorType(enum.IntEnum):
+    NoColor = 0
+    RGB8 = 1
+    Gray32 = 2
+
+
+class TSDFVolume:
+    pass
+
+
+class UniformTSDFVolume(TSDFVolume):
+    def __init__(self, length, resolution, sdf_trunc, color_type=TSDFVolumeColorType.RGB8, origin=(0.0, 0.0, 0.0),
+                 z_range=None, device=None):
+        self.length = float(length)
+        self.resolution = int(resolution)
+        self.sdf_trunc = float(sdf_trunc)
+        self.color_type = TSDFVolumeColorType(int(color_type))
+        self.origin = np.ascontiguousarray(origin, np.float64).reshape(3)
+        self.voxel_length = self.length / self.resolution
+        if self.resolution <= 0 or self.length <= 0 or self.sdf_trunc <= 0:
+            raise RuntimeError("UniformTSDFVolume: length, resolution and sdf_trunc must be positive")
+        zb, ze = (0, self.resolution) if z_range is None else (int(z_range[0]), int(z_range[1]))
+        if not (0 <= zb <= ze <= self.resolution):
+            raise RuntimeError("UniformTSDFVolume: bad z_range %r" % (z_range,))
+        self.z_begin, self.z_end = zb, ze
+        self._ctx = runtime.ctx(device)
+        t = runtime.torch()
+        R = self.resolution
+        planes = (ze - zb) + _lib.PAD_LO + _lib.PAD_HI
+        # {tsdf, weight} pairs (8 B/voxel) + packed colour (4 B/voxel), z-slowest / y-fastest
+        self._tsdfw = t.zeros((planes, R, R, 2), dtype=t.float32, device=self._ctx.tdev)
+        self._color = None
+        if self.color_type != TSDFVolumeColorType.NoColor:
+            self._color = t.zeros((planes, R, R), dtype=t.int32, device=self._ctx.tdev)
+        self._desc = _lib.Volume(R, zb, ze, int(self.color_type), self.voxel_length, self.sdf_trunc,
+                                 (C.c_double * 3)(*self.origin), self._tsdfw.data_ptr(),
+                                 0 if self._color is None else self._color.data_ptr())
+        self._updates = t.zeros(1, dtype=t.int64, device=self._ctx.tdev)
+        self.count_updates = False
+
+    # ------------------------------------------------------------------ integrate
+    def integrate(self, image, intrinsic, extrinsic):
+        """Open3D UniformTSDFVolume.integrate(rgbd, intrinsic, extrinsic); extrinsic = world->camera."""
+        depth = geometry._depth_f32_device(image)
+        H, W = int(depth.shape[0]), int(depth.shape[1])
+        if (W, H) != (intrinsic.width, intrinsic.height):
+            raise RuntimeError("[UniformTSDFVolume::Integrate] Unsupported image format.")
+        dcol = None
+        if self.color_type == TSDFVolumeColorType.RGB8:
+            col = image.color
+            if col.num_of_channels != 3 or col.bytes_per_channel != 1 or (col.width, col.height) != (W, H):
+                raise RuntimeError("[UniformTSDFVolume::Integrate] Unsupported image format.")
+            dcol = col.device_tensor()
+        elif self.color_type == TSDFVolumeColorType.Gray32:
+            col = image.color
+            if col.num_of_channels != 1 or col.bytes_per_channel != 4 or (col.width, col.height) != (W, H):
+                raise RuntimeError("[UniformTSDFVolume::Integrate] Unsupported image format.")
+            dcol = col.device_tensor()
+        self.integrate_device(depth, dcol, intrinsic, extrinsic)
+
+    def integrate_device(self, depth_f32, color, intrinsic, extrinsic):
+        """Same with frame buffers already resident in HBM (torch CUDA tensors)."""
+        c = self._ctx
+        _, ext = runtime.mat16(extrinsic)
+        K = intrinsic._c()
+        upd = runtime.ptr(self._updates) if self.count_updates else C.c_void_p(0)
+        _lib.check(_lib.load().b2r_integrate(c.handle, C.byref(self._desc), runtime.ptr(depth_f32), runtime.ptr(color),
+                                             C.byref(K), ext, upd, c.stream()))
+
+    def integrate_host(self, depth, color, intrinsic, extrinsic, depth_scale=1000.0, depth_trunc=3.0):
+        """End-to-end entry: raw HOST frame (numpy or pinned torch CPU tensors: depth uint8/uint16/float32,
+        colour uint8 [H,W,3]) -> H2D copy + depth conversion (stitcher.py:40-41 constants) + integrate."""
+        c = self._ctx
+        t = runtime.torch()
+        dt = {t.uint8: 0, t.uint16: 1, t.float32: 2}
+        if isinstance(depth, np.ndarray):
+            depth = t.from_numpy(np.ascontiguousarray(depth))
+        if isinstance(color, np.ndarray):
+            color = t.from_numpy(np.ascontiguousarray(color))
+        if depth.dtype not in dt:
+            raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
+        _, ext = runtime.mat16(extrinsic)
+        K = intrinsic._c()
+        upd = runtime.ptr(self._updates) if self.count_updates else C.c_void_p(0)
+        _lib.check(_lib.load().b2r_integrate_host(c.handle, C.byref(self._desc), C.c_void_p(depth.data_ptr()),
+                                                  dt[depth.dtype], C.c_void_p(0 if color is None else color.data_ptr()),
+                                                  C.byref(K), ext, float(depth_scale), float(depth_trunc), upd,
+                                                  c.stream()))
+
+    def updates(self):
+        """Number of voxel updates counted since the last reset (needs count_updates=True)."""
+        return int(self._updates.item())
+
+    def reset(self):
+        c = self._ctx
+        _lib.check(_lib.load().b2r_volume_reset(c.handle, C.byref(self._desc), c.stream()))
+        self._updates.zero_()
+
+    # ------------------------------------------------------------------ raw access (tests, persistence)
+    def export_arrays(self):
+        """(tsdf, weight, color) as numpy in Open3D order [x, y, z_local]; colour [.., 3] in 0..255 or None."""
+        c = self._ctx
+        t = runtime.torch()
+        R, nz = self.resolution, self.z_end - self.z_begin
+        ts = t.empty((R, R, nz), dtype=t.float32, device=c.tdev)
+        w = t.empty((R, R, nz), dtype=t.float32, device=c.tdev)
+        col = t.empty((R, R, nz, 3), dtype=t.float32, device=c.tdev) if self._color is not None else None
+        _lib.check(_lib.load().b2r_volume_export(c.handle, C.byref(self._desc), runtime.ptr(ts), runtime.ptr(w),
+                                                 runtime.ptr(col), c.stream()))
+        return ts.cpu().numpy(), w.cpu().numpy(), (None if col is None else col.cpu().numpy())
+
+    def import_arrays(self, tsdf, weight, color=None):
+        c = self._ctx
+        t = runtime.torch()
+        R, nz = self.resolution, self.z_end - self.z_begin
+        ts = runtime.to_device(np.ascontiguousarray(tsdf, np.float32).reshape(R, R, nz))
+        w = runtime.to_device(np.ascontiguousarray(weight, np.float32).reshape(R, R, nz))
+        col = None if color is None else runtime.to_device(np.ascontiguousarray(color, np.float32).reshape(R, R, nz, 3))
+        _lib.check(_lib.load().b2r_volume_import(c.handle, C.byref(self._desc), runtime.ptr(ts), runtime.ptr(w),
+                                                 runtime.ptr(col), c.stream()))
+        c.sync()
+
+    def save(self, path):
+        """Persist the slab (checkpoint/resume of the volume)."""
+        ts, w, col = self.export_arrays()
+        np.savez(path, tsdf=ts, weight=w, color=(np.zeros(0) if col is None else col), length=self.length,
+                 resolution=self.resolution, sdf_trunc=self.sdf_trunc, color_type=int(self.color_type),
+                 origin=self.origin, z_range=np.array([self.z_begin, self.z_end]))
+
+    @staticmethod
+    def load(path, device=None):
+        d = np.load(path)
+        v = UniformTSDFVolume(float(d["length"]), int(d["resolution"]), float(d["sdf_trunc"]),
+                              TSDFVolumeColorType(int(d["color_type"])), d["origin"],
+                              z_range=tuple(int(x) for x in d["z_range"]), device=device)
+        v.import_arrays(d["tsdf"], d["weight"], d["color"] if d["color"].size else None)
+        return v
+
+    # ------------------------------------------------------------------ extraction
+    def _mesh_count(self):
+        c = self._ctx
+        nv, nt = C.c_int64(0), C.c_int64(0)
+        _lib.check(_lib.load().b2r_extract_mesh_count(c.handle, C.byref(self._desc), C.byref(nv), C.byref(nt),
+                                                      c.stream()))
+        return nv.value, nt.value
+
+    def _mesh_vertices(self, nv, vertex_base=0):
+        c = self._ctx
+        t = runtime.torch()
+        V = t.empty((nv, 3), dtype=t.float64, device=c.tdev)
+        Cc = t.empty((nv, 3), dtype=t.float64, device=c.tdev) if self._color is not None else None
+        _lib.check(_lib.load().b2r_extract_mesh_vertices(c.handle, C.byref(self._desc), int(vertex_base), runtime.ptr(V),
+                                                         runtime.ptr(Cc), c.stream()))
+        return V, Cc
+
+    def _mesh_triangles(self, nt):
+        c = self._ctx
+        t = runtime.torch()
+        T = t.empty((nt, 3), dtype=t.int32, device=c.tdev)
+        _lib.check(_lib.load().b2r_extract_mesh_triangles(c.handle, C.byref(self._desc), runtime.ptr(T), c.stream()))
+        return T
+
+    def extract_triangle_mesh_device(self):
+        """(vertices f64[V,3], triangles i32[T,3], colors f64[V,3]|None) as CUDA tensors."""
+        nv, nt = self._mesh_count()
+        V, Cc = self._mesh_vertices(nv)
+        T = self._mesh_triangles(nt)
+        return V, T, Cc
+
+    def extract_triangle_mesh(self):
+        """Open3D UniformTSDFVolume.extract_triangle_mesh().  Vertex ORDER differs from
+        Open3D's first-touch scan order (ours is memory order); the vertex/triangle SETS are identical."""
+        V, T, Cc = self.extract_triangle_mesh_device()
+        m = geometry.TriangleMesh()
+        m.vertices = V.cpu().numpy()
+        m.triangles = T.cpu().numpy()
+        if Cc is not None:
+            m.vertex_colors = Cc.cpu().numpy()
+        return m
+
+    def extract_point_cloud_device(self):
+        c = self._ctx
+        t = runtime.torch()
+        n = C.c_int64(0)
+        _lib.check(_lib.load().b2r_extract_points_count(c.handle, C.byref(self._desc), C.byref(n), c.stream()))
+        n = n.value
+        P = t.empty((n, 3), dtype=t.float64, device=c.tdev)
+        N = t.empty((n, 3), dtype=t.float64, device=c.tdev)
+        Cc = t.empty((n, 3), dtype=t.float64, device=c.tdev) if self._color is not None else None
+        _lib.check(_lib.load().b2r_extract_points_emit(c.handle, C.byref(self._desc), runtime.ptr(P), runtime.ptr(N),
+                                                       runtime.ptr(Cc), c.stream()))
+        return P, N, Cc
+
+    def extract_point_cloud(self):
+        """Open3D UniformTSDFVolume.extract_point_cloud()."""
+        P, N, Cc = self.extract_point_cloud_device()
+        pcd = geometry.PointCloud()
+        pcd._p.set_dev(P)
+        pcd._n.set_dev(N)
+        if Cc is not None:
+            pcd._c.set_dev(Cc)
+        return pcd

@@ -1,0 +1,90 @@
+"""Device runtime: one library context per (process, device); PyTorch only owns device memory and
+streams (tensors are passed to the C ABI as raw `data_ptr()`s)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _lib
+
+_ctxs = {}
+
+
+def torch():
+    import torch as _t
+    return _t
+
+
+def default_device():
+    """One process per GPU: LOCAL_RANK selects the device (torchrun), else cuda:0."""
+    return int(os.environ.get("LOCAL_RANK", "0"))
+
+
+class Context:
+    def __init__(self, device):
+        t = torch()
+        if not t.cuda.is_available():
+            raise _lib.B2RError("b200recon needs a CUDA device (B200, sm_100a); none is visible and there is no "
+                                "CPU fallback")
+        self.device = int(device)
+        self.tdev = t.device("cuda", self.device)
+        t.cuda.set_device(self.device)
+        t.zeros(1, device=self.tdev)  # make sure the primary context exists
+        h = C.c_void_p()
+        _lib.check(_lib.load().b2r_ctx_create(self.device, C.byref(h)))
+        self.handle = h
+        self.updates = t.zeros(1, dtype=t.int64, device=self.tdev)
+
+    def stream(self):
+        return C.c_void_p(torch().cuda.current_stream(self.tdev).cuda_stream)
+
+    def launch_count(self):
+        n = C.c_int64(0)
+        _lib.check(_lib.load().b2r_ctx_launch_count(self.handle, C.byref(n)))
+        return n.value
+
+    def kernel_timing(self, enable):
+        _lib.check(_lib.load().b2r_ctx_kernel_timing(self.handle, int(bool(enable))))
+
+    def kernel_time(self):
+        """(total ms, launches) of the tsdf_integrate kernel since kernel_timing(True) (CUDA events)."""
+        ms, n = C.c_double(0), C.c_int64(0)
+        _lib.check(_lib.load().b2r_ctx_kernel_time(self.handle, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def sync(self):
+        _lib.check(_lib.load().b2r_ctx_sync(self.handle, self.stream()))
+
+
+def ctx(device=None):
+    d = default_device() if device is None else int(device)
+    c = _ctxs.get(d)
+    if c is None:
+        c = Context(d)
+        _ctxs[d] = c
+    return c
+
+
+def ptr(tensor):
+    return C.c_void_p(0 if tensor is None else tensor.data_ptr())
+
+
+def mat16(m):
+    a = np.ascontiguousarray(np.asarray(m, dtype=np.float64).reshape(4, 4))
+    return a, a.ctypes.data_as(_lib.c_dp)
+
+
+def to_device(array, dtype=None, device=None):
+    """numpy (or tensor) -> contiguous CUDA tensor on the context's device."""
+    t = torch()
+    c = ctx(device)
+    if isinstance(array, t.Tensor):
+        x = array
+        if dtype is not None:
+            x = x.to(dtype)
+        return x.to(c.tdev).contiguous()
+    a = np.ascontiguousarray(array)
+    x = t.from_numpy(a)
+    if dtype is not None:
+        x = x.to(dtype)
+    return x.to(c.tdev)

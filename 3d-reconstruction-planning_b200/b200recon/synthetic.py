@@ -57,3 +57,65 @@ def extrinsic_from_pose(cam_to_world):
 def volume_origin(length):
     """cube of side L with the ground plane z=0 inside, object at the xy centre."""
     return np.array([-0.5 * length, -0.5 * length, -0.1 * length])
+
+
+# ---------------------------------------------------------------------------------------------------
+# device ray caster (b2r_raycast_scene)
+# ---------------------------------------------------------------------------------------------------
+def make_scene(cam_to_world, K, ell_c=ELLIPSOID_C, ell_r=ELLIPSOID_R, plane_z=0.0, has_plane=True, checker=0.04,
+               depth_scale=1000.0, tris=None):
+    """Fill the C scene struct (float32 parameters, identical to the oracle twin's inputs)."""
+    from . import _lib
+    sc = _lib.Scene()
+    m = np.asarray(cam_to_world, np.float64)[:3, :4].astype(np.float32).reshape(-1)
+    for i in range(12):
+        sc.c2w[i] = float(m[i])
+    sc.fx, sc.fy, sc.cx, sc.cy = [float(np.float32(K[k])) for k in ("fx", "fy", "cx", "cy")]
+    sc.W, sc.H = int(K["width"]), int(K["height"])
+    for i in range(3):
+        sc.ell_c[i] = float(np.float32(ell_c[i]))
+        sc.ell_r[i] = float(np.float32(ell_r[i]))
+    sc.plane_z = float(np.float32(plane_z))
+    sc.has_plane = int(bool(has_plane))
+    sc.checker = float(np.float32(checker))
+    sc.depth_scale = float(np.float32(depth_scale))
+    sc.n_tris = 0
+    if tris is not None:
+        tr = np.ascontiguousarray(tris, np.float32).reshape(-1, 9)
+        sc.n_tris = len(tr)
+        mn, mx = tr.reshape(-1, 3).min(0), tr.reshape(-1, 3).max(0)
+        for i in range(3):
+            sc.mesh_min[i] = float(mn[i])
+            sc.mesh_max[i] = float(mx[i])
+    return sc
+
+
+def render_frame(cam_to_world, K, tris_dev=None, tris=None, out_depth=None, out_color=None, **scene_kw):
+    """Ray-cast one frame on the GPU -> (depth uint16 [H,W], color uint8 [H,W,3]) CUDA tensors."""
+    import ctypes as C
+    from . import _lib, runtime
+    c = runtime.ctx()
+    t = runtime.torch()
+    sc = make_scene(cam_to_world, K, tris=tris, **scene_kw)
+    if tris is not None and tris_dev is None:
+        tris_dev = runtime.to_device(np.ascontiguousarray(tris, np.float32).reshape(-1, 9))
+    H, W = sc.H, sc.W
+    depth = out_depth if out_depth is not None else t.empty((H, W), dtype=t.uint16, device=c.tdev)
+    color = out_color if out_color is not None else t.empty((H, W, 3), dtype=t.uint8, device=c.tdev)
+    _lib.check(_lib.load().b2r_raycast_scene(c.handle, C.byref(sc), runtime.ptr(tris_dev), runtime.ptr(depth),
+                                             runtime.ptr(color), c.stream()))
+    return depth, color
+
+
+def load_banana_triangles(path):
+    """Triangles (float32 [T,9]) of a PLY mesh such as 011_banana/poisson/nontextured.ply, moved so that
+    its bounding box rests on z = 0 and is centred in xy."""
+    from . import io
+    m = io.read_triangle_mesh(path)
+    V = np.asarray(m.vertices).copy()
+    T = np.asarray(m.triangles)
+    mn, mx = V.min(0), V.max(0)
+    V[:, 0] -= 0.5 * (mn[0] + mx[0])
+    V[:, 1] -= 0.5 * (mn[1] + mx[1])
+    V[:, 2] -= mn[2]
+    return V[T].reshape(-1, 9).astype(np.float32)

@@ -1,0 +1,96 @@
+// Context management + error reporting for the C ABI (include/b200recon.h).
+#include <cstdarg>
+
+#include "common.cuh"
+
+namespace b2r {
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+}  // namespace b2r
+
+extern "C" {
+
+const char* b2r_last_error(void) { return b2r::g_err; }
+int b2r_version(void) { return 100; }
+
+int b2r_ctx_create(int device, b2r_ctx** out) {
+    B2R_CHECK(out != nullptr, -1, "b2r_ctx_create: out is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        b2r::set_error("b2r_ctx_create: no CUDA device available (%s); this library has no CPU fallback",
+                       cudaGetErrorString(e));
+        return -2;
+    }
+    B2R_CHECK(device >= 0 && device < n, -3, "b2r_ctx_create: device %d out of range [0,%d)", device, n);
+    B2R_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    B2R_CUDA(cudaGetDeviceProperties(&prop, device));
+    B2R_CHECK(prop.major == 10, -4, "b2r_ctx_create: device %d is sm_%d%d; this library is built for sm_100a only",
+              device, prop.major, prop.minor);
+    b2r_ctx* c = new b2r_ctx();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    if (c->small.ensure(4096)) { delete c; return -102; }
+    B2R_CUDA(cudaMemset(c->small.ptr, 0, c->small.bytes));
+    c->pinned_bytes = 1 << 16;
+    B2R_CUDA(cudaMallocHost(&c->pinned, c->pinned_bytes));
+    *out = c;
+    return 0;
+}
+
+int b2r_ctx_destroy(b2r_ctx* c) {
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    b2r::Scratch* all[] = {&c->frame_dm, &c->frame_rgba, &c->frame_raw_depth, &c->frame_raw_color, &c->frame_f32,
+                           &c->small, &c->scan_a, &c->scan_b, &c->mc_code, &c->mc_flags, &c->mc_block_counts,
+                           &c->mc_vert_id, &c->pc_block_counts, &c->icp_a, &c->icp_b, &c->icp_c, &c->icp_d,
+                           &c->icp_e, &c->icp_f};
+    for (auto* s : all) s->release();
+    for (auto e : c->ev_pool) cudaEventDestroy(e);
+    if (c->pinned) cudaFreeHost(c->pinned);
+    delete c;
+    return 0;
+}
+
+int b2r_ctx_launch_count(b2r_ctx* c, int64_t* out) {
+    B2R_CHECK(c && out, -1, "b2r_ctx_launch_count: NULL argument");
+    *out = c->launches;
+    return 0;
+}
+
+int b2r_ctx_kernel_timing(b2r_ctx* c, int enable) {
+    B2R_CHECK(c, -1, "b2r_ctx_kernel_timing: NULL ctx");
+    c->timing = enable != 0;
+    if (enable) c->ev_used = 0;
+    return 0;
+}
+
+int b2r_ctx_kernel_time(b2r_ctx* c, double* ms_total, int64_t* n_launches) {
+    B2R_CHECK(c && ms_total && n_launches, -1, "b2r_ctx_kernel_time: NULL argument");
+    B2R_CUDA(cudaSetDevice(c->device));
+    double tot = 0.0;
+    for (size_t i = 0; i + 1 < c->ev_used; i += 2) {
+        B2R_CUDA(cudaEventSynchronize(c->ev_pool[i + 1]));
+        float ms = 0.f;
+        B2R_CUDA(cudaEventElapsedTime(&ms, c->ev_pool[i], c->ev_pool[i + 1]));
+        tot += ms;
+    }
+    *ms_total = tot;
+    *n_launches = (int64_t)(c->ev_used / 2);
+    return 0;
+}
+
+int b2r_ctx_sync(b2r_ctx* c, void* stream) {
+    B2R_CHECK(c, -1, "b2r_ctx_sync: NULL ctx");
+    B2R_CUDA(cudaSetDevice(c->device));
+    B2R_CUDA(cudaStreamSynchronize(b2r::S(stream)));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,87 @@
+// Shared internals of libb200recon.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/b200recon.h"
+
+namespace b2r {
+
+void set_error(const char* fmt, ...);
+
+#define B2R_CUDA(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t _e = (expr);                                                                \
+        if (_e != cudaSuccess) {                                                                \
+            b2r::set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return -100;                                                                        \
+        }                                                                                       \
+    } while (0)
+
+#define B2R_CHECK(cond, code, ...)                                                              \
+    do {                                                                                        \
+        if (!(cond)) { b2r::set_error(__VA_ARGS__); return (code); }                            \
+    } while (0)
+
+#define B2R_LAUNCH_CHECK(ctx)                                                                   \
+    do {                                                                                        \
+        (ctx)->launches++;                                                                      \
+        cudaError_t _e = cudaGetLastError();                                                    \
+        if (_e != cudaSuccess) {                                                                \
+            b2r::set_error("%s:%d: kernel launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); \
+            return -101;                                                                        \
+        }                                                                                       \
+    } while (0)
+
+// A grow-only device scratch buffer.
+struct Scratch {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t need) {
+        if (need <= bytes) return 0;
+        if (ptr) { cudaFree(ptr); ptr = nullptr; bytes = 0; }
+        size_t want = need + (need >> 3) + 256;
+        cudaError_t e = cudaMalloc(&ptr, want);
+        if (e != cudaSuccess) { set_error("cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e)); return -102; }
+        bytes = want;
+        return 0;
+    }
+    void release() { if (ptr) cudaFree(ptr); ptr = nullptr; bytes = 0; }
+};
+
+}  // namespace b2r
+
+struct b2r_ctx {
+    int device = 0;
+    int sm_count = 148;
+    int64_t launches = 0;
+    // frame staging (prepared frame: {depth_m, multiplier} float2 + packed RGBA)
+    b2r::Scratch frame_dm, frame_rgba, frame_raw_depth, frame_raw_color, frame_f32;
+    b2r::Scratch small;       // counters, per-frame scalars (zero-initialised on creation)
+    b2r::Scratch scan_a, scan_b;
+    // marching cubes
+    b2r::Scratch mc_code, mc_flags, mc_block_counts, mc_vert_id;
+    int64_t mc_nv = 0, mc_nt = 0;
+    int mc_R = 0, mc_zb = 0, mc_ze = 0;
+    // point extraction
+    b2r::Scratch pc_block_counts;
+    int64_t pc_n = 0;
+    // ICP
+    b2r::Scratch icp_a, icp_b, icp_c, icp_d, icp_e, icp_f;
+    // optional CUDA-event timing of the dominant kernel
+    bool timing = false;
+    std::vector<cudaEvent_t> ev_pool;
+    size_t ev_used = 0;
+    void* pinned = nullptr;   // small pinned host buffer for result read-back
+    size_t pinned_bytes = 0;
+};
+
+namespace b2r {
+static inline cudaStream_t S(void* s) { return (cudaStream_t)s; }
+static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+}  // namespace b2r

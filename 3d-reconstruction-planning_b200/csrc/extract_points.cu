@@ -1,0 +1,201 @@
+// Surface point extraction -- replaces Open3D UniformTSDFVolume::ExtractPointCloud (north_star API
+// extract_point_cloud(); arithmetic in SURVEY.md A.4): sign-change edges between valid voxels
+// (w != 0, -0.98 <= f < 0.98), interpolated position, colour, and the normalised central-difference
+// gradient of the trilinearly interpolated TSDF (half gap 0.99 voxel).  Two passes over the owned
+// voxels (count -> scan -> emit) with warp-ballot/prefix-sum compaction; output in memory order.
+#include "frame.cuh"
+#include "scan.cuh"
+
+namespace b2r {
+
+constexpr int PC_THREADS = 256;
+
+struct PcGeom {
+    int R, z_begin, z_end;
+    double vl, ox, oy, oz;
+    int color_type;
+};
+
+__device__ __forceinline__ int64_t pidx(int R, int z_begin, int x, int y, int z) {
+    return ((int64_t)(z - z_begin + B2R_PAD_LO) * R + x) * R + y;
+}
+__device__ __forceinline__ bool pc_valid(const float2 q) { return q.y != 0.0f && q.x < 0.98f && q.x >= -0.98f; }
+
+// bit a set when the edge voxel -> voxel + e_a produces a point
+__device__ __forceinline__ unsigned pc_flags(const float2* __restrict__ tsdfw, const PcGeom& G, int x, int y, int z) {
+    const int R = G.R;
+    if (x < 1 || y < 1 || z < 1 || x > R - 2 || y > R - 2 || z > R - 2) return 0u;
+    const int64_t i0 = pidx(R, G.z_begin, x, y, z);
+    const float2 q0 = __ldg(&tsdfw[i0]);
+    if (!pc_valid(q0)) return 0u;
+    unsigned f = 0;
+    if (x + 1 < R - 1) { const float2 q = __ldg(&tsdfw[i0 + R]); if (pc_valid(q) && q0.x * q.x < 0.0f) f |= 1u; }
+    if (y + 1 < R - 1) { const float2 q = __ldg(&tsdfw[i0 + 1]); if (pc_valid(q) && q0.x * q.x < 0.0f) f |= 2u; }
+    if (z + 1 < R - 1) { const float2 q = __ldg(&tsdfw[i0 + (int64_t)R * R]); if (pc_valid(q) && q0.x * q.x < 0.0f) f |= 4u; }
+    return f;
+}
+
+__global__ void __launch_bounds__(PC_THREADS) pc_count_kernel(const float2* __restrict__ tsdfw,
+                                                              const __grid_constant__ PcGeom G,
+                                                              uint32_t* __restrict__ blk_counts) {
+    __shared__ uint32_t s_c[PC_THREADS / 32];
+    const int R = G.R;
+    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int64_t t = (int64_t)blockIdx.x * PC_THREADS + threadIdx.x;
+    unsigned c = 0;
+    if (t < n) {
+        const int y = (int)(t % R), x = (int)((t / R) % R), z = G.z_begin + (int)(t / ((int64_t)R * R));
+        c = __popc(pc_flags(tsdfw, G, x, y, z));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) s_c[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned a = 0;
+        for (int w = 0; w < PC_THREADS / 32; ++w) a += s_c[w];
+        blk_counts[blockIdx.x] = a;
+    }
+}
+
+// Open3D GetTSDFAt(p): trilinear blend of the 8 surrounding tsdf values (no weight check).
+__device__ __forceinline__ double tsdf_at(const float2* __restrict__ tsdfw, const PcGeom& G, const double* p) {
+    int idx[3];
+    double r[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double g = p[k] / G.vl - 0.5;
+        idx[k] = (int)floor(g);
+        r[k] = g - (double)idx[k];
+    }
+    const int R = G.R;
+    const int64_t b = pidx(R, G.z_begin, idx[0], idx[1], idx[2]);
+    const int64_t sx = R, sy = 1, sz = (int64_t)R * R;
+    const double t000 = (double)__ldg(&tsdfw[b]).x, t001 = (double)__ldg(&tsdfw[b + sz]).x;
+    const double t010 = (double)__ldg(&tsdfw[b + sy]).x, t011 = (double)__ldg(&tsdfw[b + sy + sz]).x;
+    const double t100 = (double)__ldg(&tsdfw[b + sx]).x, t101 = (double)__ldg(&tsdfw[b + sx + sz]).x;
+    const double t110 = (double)__ldg(&tsdfw[b + sx + sy]).x, t111 = (double)__ldg(&tsdfw[b + sx + sy + sz]).x;
+    return (1 - r[0]) * ((1 - r[1]) * ((1 - r[2]) * t000 + r[2] * t001) + r[1] * ((1 - r[2]) * t010 + r[2] * t011)) +
+           r[0] * ((1 - r[1]) * ((1 - r[2]) * t100 + r[2] * t101) + r[1] * ((1 - r[2]) * t110 + r[2] * t111));
+}
+
+__global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __restrict__ tsdfw,
+                                                             const uint32_t* __restrict__ color,
+                                                             const __grid_constant__ PcGeom G,
+                                                             const uint32_t* __restrict__ blk_off,
+                                                             double* __restrict__ pts, double* __restrict__ nrm,
+                                                             double* __restrict__ cols) {
+    __shared__ uint32_t smem[33];
+    const int R = G.R;
+    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int64_t t = (int64_t)blockIdx.x * PC_THREADS + threadIdx.x;
+    unsigned f = 0;
+    int x = 0, y = 0, z = 0;
+    if (t < n) {
+        y = (int)(t % R); x = (int)((t / R) % R); z = G.z_begin + (int)(t / ((int64_t)R * R));
+        f = pc_flags(tsdfw, G, x, y, z);
+    }
+    uint32_t total;
+    const uint32_t local = block_exclusive_scan(__popc(f), smem, &total);
+    if (total == 0 || f == 0) return;
+    int64_t k = (int64_t)blk_off[blockIdx.x] + local;
+    const double hvl = 0.5 * G.vl;
+    const int64_t i0 = pidx(R, G.z_begin, x, y, z);
+    const float f0 = tsdfw[i0].x;
+    const double p0[3] = {hvl + G.vl * (double)x, hvl + G.vl * (double)y, hvl + G.vl * (double)z};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        if (!(f & (1u << a))) continue;
+        const int64_t i1 = i0 + (a == 0 ? (int64_t)R : a == 1 ? (int64_t)1 : (int64_t)R * R);
+        const float f1 = tsdfw[i1].x;
+        const float r0 = fabsf(f0), r1 = fabsf(f1);
+        double p[3] = {p0[0], p0[1], p0[2]};
+        const double p1a = p0[a] + G.vl;
+        p[a] = (p0[a] * (double)r1 + p1a * (double)r0) / (double)(r0 + r1);
+        pts[k * 3 + 0] = p[0] + G.ox;
+        pts[k * 3 + 1] = p[1] + G.oy;
+        pts[k * 3 + 2] = p[2] + G.oz;
+        if (cols && G.color_type) {
+            const uint32_t c0 = color[i0], c1 = color[i1];
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                double a0, a1, s;
+                if (G.color_type == 1) {
+                    a0 = (double)((float)((c0 >> (10 * q)) & 1023u) * 0.25f);
+                    a1 = (double)((float)((c1 >> (10 * q)) & 1023u) * 0.25f);
+                    s = 255.0;
+                } else {
+                    a0 = (double)__uint_as_float(c0); a1 = (double)__uint_as_float(c1); s = 1.0;
+                }
+                cols[k * 3 + q] = (a0 * (double)r1 + a1 * (double)r0) / (double)(r0 + r1) / s;
+            }
+        }
+        // GetNormalAt(p): n(i) = GetTSDFAt(p + gap e_i) - GetTSDFAt(p - gap e_i), normalised
+        const double half_gap = 0.99 * G.vl;
+        double nv[3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            double pp[3] = {p[0], p[1], p[2]};
+            pp[q] -= half_gap;
+            const double t0 = tsdf_at(tsdfw, G, pp);
+            pp[q] += 2 * half_gap;
+            const double t1 = tsdf_at(tsdfw, G, pp);
+            nv[q] = t1 - t0;
+        }
+        const double nn = sqrt(nv[0] * nv[0] + nv[1] * nv[1] + nv[2] * nv[2]);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) nrm[k * 3 + q] = nn > 0 ? nv[q] / nn : nv[q];
+        ++k;
+    }
+}
+
+}  // namespace b2r
+
+using namespace b2r;
+
+extern "C" {
+
+int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_points, void* stream) {
+    B2R_CHECK(ctx && vol && vol->d_tsdfw && n_points, -1, "b2r_extract_points_count: NULL argument");
+    B2R_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = S(stream);
+    const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
+    *n_points = 0;
+    ctx->pc_n = 0;
+    if (nz <= 0 || R < 3) return 0;
+    const int64_t n = (int64_t)nz * R * R;
+    const int nblocks = cdiv(n, PC_THREADS);
+    if (ctx->pc_block_counts.ensure((size_t)nblocks * sizeof(uint32_t))) return -102;
+    uint32_t* blk = (uint32_t*)ctx->pc_block_counts.ptr;
+    PcGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
+             vol->color_type};
+    pc_count_kernel<<<nblocks, PC_THREADS, 0, st>>>((const float2*)vol->d_tsdfw, G, blk);
+    B2R_LAUNCH_CHECK(ctx);
+    unsigned long long* tot = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64_C;
+    if (int rc = scan_exclusive_u32(ctx, blk, blk, nblocks, tot, st)) return rc;
+    B2R_CUDA(cudaMemcpyAsync(ctx->pinned, tot, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    B2R_CUDA(cudaStreamSynchronize(st));
+    ctx->pc_n = (int64_t) * (unsigned long long*)ctx->pinned;
+    *n_points = ctx->pc_n;
+    return 0;
+}
+
+int b2r_extract_points_emit(b2r_ctx* ctx, const b2r_volume* vol, double* d_points, double* d_normals,
+                            double* d_colors, void* stream) {
+    B2R_CHECK(ctx && vol && vol->d_tsdfw, -1, "b2r_extract_points_emit: NULL argument");
+    B2R_CUDA(cudaSetDevice(ctx->device));
+    const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
+    if (nz <= 0 || R < 3 || ctx->pc_n == 0) return 0;
+    B2R_CHECK(d_points && d_normals, -1, "b2r_extract_points_emit: NULL output");
+    const int64_t n = (int64_t)nz * R * R;
+    const int nblocks = cdiv(n, PC_THREADS);
+    PcGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
+             vol->color_type};
+    pc_emit_kernel<<<nblocks, PC_THREADS, 0, S(stream)>>>((const float2*)vol->d_tsdfw, (const uint32_t*)vol->d_color, G,
+                                                          (const uint32_t*)ctx->pc_block_counts.ptr, d_points,
+                                                          d_normals, vol->color_type ? d_colors : nullptr);
+    B2R_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+}  // extern "C"

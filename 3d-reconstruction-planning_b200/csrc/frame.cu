@@ -1,0 +1,207 @@
+// Frame-side kernels: depth conversion, frame preparation for integration
+// ({depth, distance-multiplier} float2 image + packed colour, A.3), ordered back-projection (A.2).
+// Reference call sites: stitcher.py:34-46.
+#include "frame.cuh"
+#include "scan.cuh"
+
+namespace b2r {
+
+__device__ __forceinline__ float load_depth_raw(const void* depth, int dtype, int64_t i) {
+    if (dtype == 0) return (float)((const uint8_t*)depth)[i] / 255.0f;
+    if (dtype == 1) return (float)((const uint16_t*)depth)[i];
+    return ((const float*)depth)[i];
+}
+
+// O3D Image::ConvertDepthToFloatImage: p /= (float)scale; if (p >= (float)trunc) p = 0.
+__global__ void depth_to_float_kernel(const void* __restrict__ depth, int dtype, int64_t n, float scale, float trunc,
+                                      float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float p = load_depth_raw(depth, dtype, i);
+    p = p / scale;
+    if (p >= trunc) p = 0.0f;
+    out[i] = p;
+}
+
+// One pass per frame: metres depth (optionally converting from the raw dtype), the
+// depth->camera-distance multiplier of O3D CreateDepthToCameraDistanceMultiplierFloatImage
+// (float32, sqrtf(xx^2 + yy^2 + 1), same operation order) interleaved as float2 so the integrate
+// kernel fetches both with one 8-byte gather; colour packed to one 32-bit word per pixel.
+__global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, int convert, float scale, float trunc,
+                                     const void* __restrict__ color, int color_mode, int H, int W, float cx, float cy,
+                                     float ffl_inv_x, float ffl_inv_y, float2* __restrict__ dm,
+                                     uint32_t* __restrict__ rgba, unsigned int* __restrict__ dmax_bits) {
+    const int u = blockIdx.x * blockDim.x + threadIdx.x;
+    const int v = blockIdx.y;
+    float d = 0.0f;
+    if (u < W) {
+        const int64_t i = (int64_t)v * W + u;
+        d = load_depth_raw(depth, dtype, i);
+        if (convert) {
+            d = d / scale;
+            if (d >= trunc) d = 0.0f;
+        }
+        const float xx = ((float)u - cx) * ffl_inv_x;
+        const float yy = ((float)v - cy) * ffl_inv_y;
+        const float m = sqrtf(xx * xx + yy * yy + 1.0f);
+        dm[i] = make_float2(d, m);
+        if (color_mode == 1) {
+            const uint8_t* p = (const uint8_t*)color + i * 3;
+            rgba[i] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+        } else if (color_mode == 2) {
+            rgba[i] = __float_as_uint(((const float*)color)[i]);
+        }
+    }
+    // frame-wide maximum depth (positive floats order like their bit patterns)
+    float m = (d > 0.0f) ? d : 0.0f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.0f) atomicMax(dmax_bits, __float_as_uint(m));
+}
+
+int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
+                  const void* d_color, int color_mode, const b2r_intrinsic* K, cudaStream_t stream) {
+    const int H = K->height, W = K->width;
+    const size_t n = (size_t)H * W;
+    if (ctx->frame_dm.ensure(n * sizeof(float2))) return -102;
+    if (ctx->frame_rgba.ensure(n * sizeof(uint32_t))) return -102;
+    unsigned int* dmax = (unsigned int*)ctx->small.ptr + SMALL_DMAX;
+    B2R_CUDA(cudaMemsetAsync(dmax, 0, sizeof(unsigned int), stream));
+    const float ffl_inv_x = 1.0f / (float)K->fx, ffl_inv_y = 1.0f / (float)K->fy;
+    dim3 block(128), grid(cdiv(W, 128), H);
+    frame_prepare_kernel<<<grid, block, 0, stream>>>(d_depth, dtype, convert, (float)depth_scale, (float)depth_trunc,
+                                                     d_color, color_mode, H, W, (float)K->cx, (float)K->cy, ffl_inv_x,
+                                                     ffl_inv_y, (float2*)ctx->frame_dm.ptr,
+                                                     (uint32_t*)ctx->frame_rgba.ptr, dmax);
+    B2R_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Back-projection with order-preserving compaction (row-major pixel order, invalid dropped).
+// ---------------------------------------------------------------------------------------------
+constexpr int BP_THREADS = 256;
+
+__global__ void __launch_bounds__(BP_THREADS) backproject_count_kernel(const float* __restrict__ depth, int64_t n,
+                                                                       uint32_t* __restrict__ block_counts) {
+    const int64_t i = (int64_t)blockIdx.x * BP_THREADS + threadIdx.x;
+    const bool valid = (i < n) && (depth[i] > 0.0f);
+    const int c = __syncthreads_count(valid);
+    if (threadIdx.x == 0) block_counts[blockIdx.x] = (uint32_t)c;
+}
+
+struct BackprojectParams {
+    double pose[12];  // camera->world rows 0..2
+    double fx, fy, cx, cy;
+    int W, nc;
+};
+
+__global__ void __launch_bounds__(BP_THREADS) backproject_emit_kernel(const float* __restrict__ depth,
+                                                                      const uint8_t* __restrict__ color, int64_t n,
+                                                                      const __grid_constant__ BackprojectParams P,
+                                                                      const uint32_t* __restrict__ block_offsets,
+                                                                      double* __restrict__ pts, double* __restrict__ cols) {
+    __shared__ uint32_t warp_counts[BP_THREADS / 32];
+    const int64_t i = (int64_t)blockIdx.x * BP_THREADS + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float d = 0.0f;
+    if (i < n) d = depth[i];
+    const bool valid = d > 0.0f;
+    const unsigned ballot = __ballot_sync(0xffffffffu, valid);
+    if (lane == 0) warp_counts[warp] = __popc(ballot);
+    __syncthreads();
+    uint32_t off = block_offsets[blockIdx.x];
+    for (int w = 0; w < warp; ++w) off += warp_counts[w];
+    off += __popc(ballot & ((1u << lane) - 1u));
+    if (!valid) return;
+    const int row = (int)(i / P.W), col = (int)(i % P.W);
+    const double z = (double)d;
+    const double x = (col - P.cx) * z / P.fx;
+    const double y = (row - P.cy) * z / P.fy;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+        pts[(int64_t)off * 3 + r] = ((P.pose[r * 4 + 0] * x + P.pose[r * 4 + 1] * y) + P.pose[r * 4 + 2] * z) + P.pose[r * 4 + 3];
+    if (color && cols) {
+        const uint8_t* pc = color + i * P.nc;
+        cols[(int64_t)off * 3 + 0] = pc[0] / 255.0;
+        cols[(int64_t)off * 3 + 1] = pc[(P.nc - 1) / 2] / 255.0;
+        cols[(int64_t)off * 3 + 2] = pc[P.nc - 1] / 255.0;
+    }
+}
+
+// 4x4 inverse on the host (double, Gauss-Jordan with partial pivoting).
+void invert4(const double* m, double* out) {
+    double a[4][8];
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            a[i][j] = m[i * 4 + j];
+            a[i][4 + j] = (i == j) ? 1.0 : 0.0;
+        }
+    for (int c = 0; c < 4; ++c) {
+        int p = c;
+        for (int r = c + 1; r < 4; ++r)
+            if (fabs(a[r][c]) > fabs(a[p][c])) p = r;
+        if (p != c)
+            for (int j = 0; j < 8; ++j) { double t = a[p][j]; a[p][j] = a[c][j]; a[c][j] = t; }
+        const double d = a[c][c];
+        for (int j = 0; j < 8; ++j) a[c][j] /= d;
+        for (int r = 0; r < 4; ++r) {
+            if (r == c) continue;
+            const double f = a[r][c];
+            if (f != 0.0)
+                for (int j = 0; j < 8; ++j) a[r][j] -= f * a[c][j];
+        }
+    }
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) out[i * 4 + j] = a[i][4 + j];
+}
+
+}  // namespace b2r
+
+using namespace b2r;
+
+extern "C" {
+
+int b2r_depth_to_float(b2r_ctx* ctx, const void* d_depth, int dtype, int H, int W, double depth_scale,
+                       double depth_trunc, float* d_out, void* stream) {
+    B2R_CHECK(ctx && d_depth && d_out, -1, "b2r_depth_to_float: NULL argument");
+    B2R_CHECK(dtype >= 0 && dtype <= 2, -5, "b2r_depth_to_float: unsupported depth dtype %d", dtype);
+    B2R_CUDA(cudaSetDevice(ctx->device));
+    const int64_t n = (int64_t)H * W;
+    if (n == 0) return 0;
+    depth_to_float_kernel<<<cdiv(n, 256), 256, 0, S(stream)>>>(d_depth, dtype, n, (float)depth_scale,
+                                                               (float)depth_trunc, d_out);
+    B2R_LAUNCH_CHECK(ctx);
+    return 0;
+}
+
+int b2r_backproject(b2r_ctx* ctx, const float* d_depth, const uint8_t* d_color, int nc, const b2r_intrinsic* K,
+                    const double* extrinsic, double* d_points, double* d_colors, int64_t* n_points, void* stream) {
+    B2R_CHECK(ctx && d_depth && K && extrinsic && d_points && n_points, -1, "b2r_backproject: NULL argument");
+    B2R_CHECK(!d_color || nc == 3 || nc == 4, -5, "b2r_backproject: colour must have 3 or 4 channels, got %d", nc);
+    B2R_CUDA(cudaSetDevice(ctx->device));
+    const int64_t n = (int64_t)K->width * K->height;
+    *n_points = 0;
+    if (n == 0) return 0;
+    const int nblocks = cdiv(n, BP_THREADS);
+    if (ctx->scan_a.ensure((size_t)nblocks * sizeof(uint32_t))) return -102;
+    uint32_t* counts = (uint32_t*)ctx->scan_a.ptr;
+    unsigned long long* total = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64;
+    cudaStream_t st = S(stream);
+    backproject_count_kernel<<<nblocks, BP_THREADS, 0, st>>>(d_depth, n, counts);
+    B2R_LAUNCH_CHECK(ctx);
+    if (int rc = scan_exclusive_u32(ctx, counts, counts, nblocks, total, st)) return rc;
+    BackprojectParams P;
+    double pose[16];
+    invert4(extrinsic, pose);
+    for (int i = 0; i < 12; ++i) P.pose[i] = pose[i];
+    P.fx = K->fx; P.fy = K->fy; P.cx = K->cx; P.cy = K->cy; P.W = K->width; P.nc = nc;
+    backproject_emit_kernel<<<nblocks, BP_THREADS, 0, st>>>(d_depth, d_color, n, P, counts, d_points, d_colors);
+    B2R_LAUNCH_CHECK(ctx);
+    B2R_CUDA(cudaMemcpyAsync(ctx->pinned, total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    B2R_CUDA(cudaStreamSynchronize(st));
+    *n_points = (int64_t) * (unsigned long long*)ctx->pinned;
+    return 0;
+}
+
+}  // extern "C"

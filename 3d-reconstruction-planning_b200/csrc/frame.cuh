@@ -1,0 +1,20 @@
+#pragma once
+#include "common.cuh"
+
+namespace b2r {
+
+// slots inside ctx->small (uint32 index for 32-bit values, uint64 index for 64-bit values; the two
+// index spaces are kept apart: 32-bit slots live in bytes [0,1024), 64-bit slots in [1024,4096)).
+constexpr int SMALL_DMAX = 0;          // uint32: bits of the frame's max depth
+constexpr int SMALL_TOTAL64 = 128;     // uint64 index (byte 1024): scan totals
+constexpr int SMALL_TOTAL64_B = 129;
+constexpr int SMALL_TOTAL64_C = 130;
+
+// Fills ctx->frame_dm (float2 {depth_m, multiplier}) and ctx->frame_rgba for one frame.
+// color_mode: 0 none, 1 uint8 x3, 2 float32 gray.
+int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
+                  const void* d_color, int color_mode, const b2r_intrinsic* K, cudaStream_t stream);
+
+void invert4(const double* m, double* out);
+
+}  // namespace b2r

@@ -1,0 +1,342 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the reconstruction hot path (BASELINE.json metric:
+"TSDF frames/s & voxel-updates/s (1-8 B200, %HBM peak); ICP pairs/s").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload tsdf1024|tsdf512] [--impl b200|reference]
+
+A "step" is the integration of ONE synthetic 640x480 RGB-D frame of the orbit into the dense TSDF+colour
+volume.  Default workload `tsdf1024` = BASELINE config[2] (1024^3 @ 2 mm, 256-frame orbit; the size the
+north_star target is quoted on, and it fits one B200: 12.9 GB); `tsdf512` = config[1] (512^3, 64 frames).
+For N > 1 (torchrun, one rank per GPU) the cube is z-slab sharded: every rank integrates every frame
+into its own slab, no data-path collective -> total work fixed -> "scaling": "strong".
+
+  value     frames/s with the frames already resident in HBM (ray-cast on the GPU before timing).
+  e2e       frames/s through the public API with HOST (pinned) uint16 depth + uint8 colour frames:
+            H2D copies + depth conversion inside the timed region, 8-byte D2H result per step.
+  roofline  tsdf_integrate kernel alone: CUDA events on the launching stream around every launch;
+            achieved = (voxel-updates * 24 B + frame bytes) / duration vs MEASURED_PEAKS.json hbm_gbs.
+  cpu_baseline / --impl reference: the oracle (C++/OpenMP restatement of Open3D's integrate -- the
+            reference's own CPU path, Open3D 0.18, cannot be installed here) on the box's host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "3d-reconstruction-planning_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (resolution, length m, sdf_trunc m, orbit frames, orbit radius m)   SURVEY.md 8(d)
+    "tsdf512": (512, 1.024, 0.01, 64, 0.5),
+    "tsdf1024": (1024, 2.048, 0.01, 256, 0.9),
+}
+B_UPD = 24  # algorithmic bytes per voxel update: float2 R+W (16) + packed colour R+W (8)  
+
+
+def frame_bytes(K):
+    n = K["width"] * K["height"]
+    return n * (8 + 4)  # prepared {depth,multiplier} float2 + packed colour, read once per launch
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, device):
+        self.device = device
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        self.t = threading.Thread(target=self._read, daemon=True)
+        self.t.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def orbit(workload):
+    from b200recon import synthetic as syn
+    R, L, trunc, nf, radius = WORKLOADS[workload]
+    poses = syn.orbit_poses(nf, radius=radius, elevation_deg=30.0)
+    return R, L, trunc, poses
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle on the host cores (cpu_baseline and --impl reference)
+# ------------------------------------------------------------------------------------------------
+def cpu_frames(workload, n, K):
+    from b200recon import synthetic as syn
+    from oracle import oracle as orc
+    R, L, trunc, poses = orbit(workload)
+    kt = (K["fx"], K["fy"], K["cx"], K["cy"])
+    stride = max(1, len(poses) // n)
+    out = []
+    for p in poses[::stride][:n]:
+        d16, rgb = orc.raycast_scene(p, kt, K["width"], K["height"])
+        out.append((orc.depth_to_float(d16), rgb, syn.extrinsic_from_pose(p)))
+    return out
+
+
+def cpu_volume(workload):
+    """Oracle volume over the largest x-range that fits comfortably in host RAM (Open3D parallelises
+    Integrate over x, so an x-range is the natural linear sample); returns (vol, scale)."""
+    from b200recon import synthetic as syn
+    from oracle import oracle as orc
+    R, L, trunc, _ = orbit(workload)
+    try:
+        avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
+    except Exception:
+        avail = 8 << 30
+    per_x = R * R * 32  # tsdf f32 + weight f32 + colour 3 x f64
+    nx = int(min(R, max(8, (min(avail // 3, 6 << 30)) // per_x)))
+    x0 = (R - nx) // 2  # centred range: the orbit looks at the cube centre
+    vol = orc.UniformTSDFVolume(L, R, trunc, 1, syn.volume_origin(L), x_range=(x0, x0 + nx))
+    return vol, R / nx, (x0, x0 + nx)
+
+
+def run_cpu(workload, steps, warmup, K, budget_s=25.0):
+    """frames/s of the oracle; each step = one frame on the sampled x-range, scaled linearly to R."""
+    kt = (K["fx"], K["fy"], K["cx"], K["cy"])
+    vol, scale, xr = cpu_volume(workload)
+    frames = cpu_frames(workload, max(1, min(8, steps)), K)
+    for i in range(max(1, warmup)):
+        d, c, e = frames[i % len(frames)]
+        vol.integrate(d, c, kt, e)
+    t0 = time.perf_counter()
+    n = upd = 0
+    while n < steps and (time.perf_counter() - t0) < budget_s:
+        d, c, e = frames[n % len(frames)]
+        upd += vol.integrate(d, c, kt, e)
+        n += 1
+    dt = time.perf_counter() - t0
+    R = WORKLOADS[workload][0]
+    fps = n / (dt * scale)
+    sample = "%d frames of %s, x-range [%d,%d) of %d (time scaled x%.2f to the full cube)" % (n, workload, xr[0], xr[1],
+                                                                                             R, scale)
+    return fps, upd / dt, n, sample, dt
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    import b200recon as o3d
+    from b200recon import runtime, synthetic as syn
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    K = syn.D435_640x480
+    kt = (K["fx"], K["fy"], K["cx"], K["cy"])
+    intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], *kt)
+    R, L, trunc, poses = orbit(args.workload)
+    ctx = runtime.ctx(local)
+    dev = ctx.tdev
+
+    # z-slab owned by this rank
+    zb, ze = R * rank // world, R * (rank + 1) // world
+    vol = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
+                                                      syn.volume_origin(L), z_range=(zb, ze), device=local)
+    vol.count_updates = True
+
+    # synthetic frames: ray-cast on this GPU (resident in HBM), raw uint16 depth + uint8 colour
+    nf = min(len(poses), max(args.steps + args.warmup, 1))
+    d16 = torch.empty((nf, K["height"], K["width"]), dtype=torch.uint16, device=dev)
+    rgb = torch.empty((nf, K["height"], K["width"], 3), dtype=torch.uint8, device=dev)
+    exts = []
+    for i in range(nf):
+        syn.render_frame(poses[i], K, out_depth=d16[i], out_color=rgb[i])
+        exts.append(syn.extrinsic_from_pose(poses[i]))
+    # device-resident arm input: float32 metres depth (what RGBDImage holds), converted outside the timed region
+    depth_f = torch.empty((nf, K["height"], K["width"]), dtype=torch.float32, device=dev)
+    from b200recon import _lib
+    import ctypes as C
+    for i in range(nf):
+        _lib.check(_lib.load().b2r_depth_to_float(ctx.handle, runtime.ptr(d16[i]), 1, K["height"], K["width"], 1000.0,
+                                                  3.0, runtime.ptr(depth_f[i]), ctx.stream()))
+    # pinned host copies for the e2e arm
+    d16_h = d16.cpu().pin_memory()
+    rgb_h = rgb.cpu().pin_memory()
+    res_h = torch.zeros(1, dtype=torch.int64).pin_memory()
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_dev(i):
+        k = i % nf
+        vol.integrate_device(depth_f[k], rgb[k], intr, exts[k])
+
+    def step_e2e(i):
+        k = i % nf
+        vol.integrate_host(d16_h[k], rgb_h[k], intr, exts[k])
+        res_h.copy_(vol._updates, non_blocking=True)   # the step's result (running update count), 8 B D2H
+
+    def timed(step, steps, warmup, sample_clocks=False):
+        vol.reset()
+        for i in range(warmup):
+            step(i)
+        barrier()
+        sampler = ClockSampler(local) if sample_clocks else None
+        if sampler:
+            sampler.start()
+        upd0 = vol.updates()
+        l0 = ctx.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(warmup, warmup + steps):
+            step(i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        clocks = sampler.stop() if sampler else None
+        upd = vol.updates() - upd0
+        launches = ctx.launch_count() - l0
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+            u = torch.tensor([upd], dtype=torch.int64, device=dev)
+            dist.all_reduce(u)
+            upd = int(u.item())
+        return ms, upd, launches, clocks
+
+    ms, upd, launches, clocks = timed(step_dev, args.steps, args.warmup, sample_clocks=True)
+    # dominant kernel alone: CUDA events around every tsdf_integrate launch (same steps again)
+    ctx.kernel_timing(True)
+    _ms2, upd_k, _, _ = timed(step_dev, args.steps, args.warmup)
+    ctx.kernel_timing(False)
+    k_ms, k_n = ctx.kernel_time()
+    k_n_timed = args.steps
+    # kernel_time covers warm-up launches too; time only the last `steps` launches' share
+    k_ms_timed = k_ms * k_n_timed / max(k_n, 1)
+    e_ms, e_upd, _, _ = timed(step_e2e, args.steps, args.warmup)
+
+    out = None
+    if rank == 0:
+        peak, peak_src = peaks()
+        nz_frac = (ze - zb) / R
+        upd_rank0_per_launch = (upd_k / world) / max(args.steps, 1)  # slabs see ~equal shares over an orbit
+        alg_bytes = upd_rank0_per_launch * B_UPD + frame_bytes(K)
+        achieved = alg_bytes / (k_ms_timed / max(args.steps, 1) * 1e-3) / 1e9
+        fps = args.steps / (ms * 1e-3)
+        out = {
+            "metric": "TSDF integration frames/s (640x480 RGB-D into dense TSDF+colour volume)",
+            "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "resolution": R, "voxel_mm": 1000.0 * L / R, "frames_in_orbit": len(poses),
+                       "frame": "640x480 uint16 depth + uint8 rgb", "sharding": "z-slab x%d" % world,
+                       "l2": "volume (%.1f GB) >> L2; consecutive frames touch overlapping voxels as in a real "
+                             "sequence, no artificial flush" % (R ** 3 * 12 / 1e9)},
+            "voxel_updates_per_s": upd / (ms * 1e-3),
+            "voxel_visits_per_s": float(R) ** 3 * fps,
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "e2e": {"value": args.steps / (e_ms * 1e-3), "unit": "frames/s",
+                    "h2d_bytes_per_step": int(d16_h[0].numel() * 2 + rgb_h[0].numel()), "d2h_bytes_per_step": 8,
+                    "voxel_updates_per_s": e_upd / (e_ms * 1e-3)},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "tsdf_integrate_kernel", "peak_source": peak_src,
+                         "kernel_ms_per_launch": k_ms_timed / max(args.steps, 1),
+                         "alg_bytes_per_launch": alg_bytes, "bytes_per_update": B_UPD,
+                         "frac_of_nominal_8TBs": achieved / 8000.0},
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="tsdf1024", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    from b200recon import synthetic as syn
+    K = syn.D435_640x480
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        fps, ups, n, sample, dt = run_cpu(args.workload, args.steps, args.warmup, K, budget_s=120.0)
+        cores = os.cpu_count()
+        R = WORKLOADS[args.workload][0]
+        print(json.dumps({
+            "impl": "reference", "metric": "TSDF integration frames/s (640x480 RGB-D into dense TSDF+colour volume)",
+            "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": n, "warmup": args.warmup,
+            "ms_per_step": 1000.0 / fps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": args.workload, "resolution": R},
+            "voxel_updates_per_s": ups,
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "reference = Open3D 0.18 CPU wheel (not installable here); timed: the oracle's C++/OpenMP "
+                    "restatement of UniformTSDFVolume::Integrate, parallelised over x like Open3D"}))
+        return
+
+    out = run_gpu(args)
+    if out is not None:
+        if not args.no_cpu_baseline and args.gpus == 1:
+            fps, ups, n, sample, dt = run_cpu(args.workload, 8, 1, K, budget_s=25.0)
+            out["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+                                   "sample": sample, "voxel_updates_per_s": ups}
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

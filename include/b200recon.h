@@ -1,0 +1,181 @@
+/*
+ * b200recon.h -- C ABI of libb200recon.so: the B200 (sm_100a) implementation of the RGB-D
+ * reconstruction hot path that the reference's stitcher.py hands to Open3D 0.18.0.
+ *
+ * Every entry point names the reference interface it replaces.  "stitcher.py:NN" is the call
+ * site in /root/reference; "O3D" is the Open3D 0.18.0 legacy API the call resolves to (the
+ * arithmetic is restated in SURVEY.md Appendix A; Open3D sources are not in /root/reference).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no C++/torch types.
+ *   - every function returns 0 on success, <0 on error; b2r_last_error() gives the message
+ *     (thread-local).  No exceptions cross the ABI.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
+ *   - pointers named d_* are DEVICE pointers owned by the caller (e.g. tensor.data_ptr());
+ *     h_* are HOST pointers.  The library owns only the scratch inside a b2r_ctx.
+ *   - calls are asynchronous on `stream` unless documented as blocking.
+ *   - transforms are row-major double[16]; `extrinsic` = world->camera as in Open3D.
+ *
+ * Volume memory layout (device, chosen for coalescing on B200 -- NOT Open3D's AoS):
+ *   slab of planes z in [z_begin, z_end) of an R x R x R cube, stored z-slowest, y-fastest with
+ *   B2R_PAD_LO halo planes below and B2R_PAD_HI above:
+ *       plane p = z - z_begin + B2R_PAD_LO,   index = (p * R + x) * R + y
+ *   tsdfw : float2 {tsdf, weight} per voxel (8 B);
+ *   color : uint32 packed 10:10:10 fixed point (value*4, R in bits 0-9, G 10-19, B 20-29).
+ */
+#ifndef B200RECON_H
+#define B200RECON_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2R_PAD_LO 1
+#define B2R_PAD_HI 2
+
+typedef struct b2r_ctx b2r_ctx;
+
+/* O3D camera.PinholeCameraIntrinsic(width,height,fx,fy,cx,cy) -- stitcher.py:264-267 */
+typedef struct b2r_intrinsic {
+    int32_t width, height;
+    double fx, fy, cx, cy;
+} b2r_intrinsic;
+
+/* O3D pipelines.integration.UniformTSDFVolume(length, resolution, sdf_trunc, color_type, origin)
+ * color_type: 0 NoColor, 1 RGB8, 2 Gray32 (TSDFVolumeColorType). */
+typedef struct b2r_volume {
+    int32_t resolution;        /* R */
+    int32_t z_begin, z_end;    /* planes owned by this slab (whole cube: 0, R) */
+    int32_t color_type;
+    double voxel_length;       /* length / resolution */
+    double sdf_trunc;
+    double origin[3];
+    void* d_tsdfw;             /* float2 [(z_end-z_begin+PAD_LO+PAD_HI) * R * R] */
+    void* d_color;             /* uint32, same count; NULL when color_type == 0 */
+} b2r_volume;
+
+/* ---- library / context ------------------------------------------------------------------ */
+const char* b2r_last_error(void);
+int b2r_version(void);
+/* One context per (process, device, logical stream of work).  Owns scratch buffers. */
+int b2r_ctx_create(int device, b2r_ctx** out);
+int b2r_ctx_destroy(b2r_ctx* ctx);
+/* Number of kernels this context has launched so far (bench.py "gpu_launches"). */
+int b2r_ctx_launch_count(b2r_ctx* ctx, int64_t* out);
+int b2r_ctx_sync(b2r_ctx* ctx, void* stream); /* blocking */
+/* Per-kernel timing of the dominant kernel (tsdf_integrate) with CUDA events recorded on the launching
+ * stream around each launch: enable=1 starts (and clears) collection, enable=0 stops it.
+ * b2r_ctx_kernel_time is blocking: total milliseconds and number of launches collected. */
+int b2r_ctx_kernel_timing(b2r_ctx* ctx, int enable);
+int b2r_ctx_kernel_time(b2r_ctx* ctx, double* ms_total, int64_t* n_launches);
+
+/* ---- images / back-projection (stitcher.py:34-46) --------------------------------------- */
+/* O3D Image.ConvertDepthToFloatImage(depth_scale, depth_trunc) inside
+ * RGBDImage.create_from_color_and_depth (stitcher.py:38-42).
+ * dtype: 0 uint8 (v/255), 1 uint16, 2 float32.  d_out: float32 [H*W] metres. */
+int b2r_depth_to_float(b2r_ctx* ctx, const void* d_depth, int dtype, int H, int W, double depth_scale,
+                       double depth_trunc, float* d_out, void* stream);
+/* O3D PointCloud.create_from_rgbd_image(rgbd, intrinsic, extrinsic) (stitcher.py:45-46).
+ * d_depth: float32 metres; d_color: uint8 [H,W,nc] (nc 3|4) or NULL.  Output in row-major pixel
+ * order with invalid (d<=0) pixels dropped: d_points/d_colors double [<=H*W,3].
+ * Blocking: returns the point count in *n_points. */
+int b2r_backproject(b2r_ctx* ctx, const float* d_depth, const uint8_t* d_color, int nc, const b2r_intrinsic* K,
+                    const double* extrinsic, double* d_points, double* d_colors, int64_t* n_points, void* stream);
+
+/* ---- TSDF integration (O3D UniformTSDFVolume.integrate(rgbd, intrinsic, extrinsic)) ------ */
+/* d_depth: float32 metres [H,W] (RGBDImage.depth); d_color: uint8 [H,W,3] (RGB8) or float32 [H,W]
+ * (Gray32) or NULL (NoColor).  d_updates (optional, uint64 on device) is incremented by the number
+ * of voxels updated. */
+int b2r_integrate(b2r_ctx* ctx, const b2r_volume* vol, const float* d_depth, const void* d_color,
+                  const b2r_intrinsic* K, const double* extrinsic, unsigned long long* d_updates, void* stream);
+/* Same, end to end from HOST frame buffers: H2D copy + depth conversion (depth_scale/depth_trunc as
+ * in stitcher.py:40-41) + integrate.  h_depth dtype as in b2r_depth_to_float.  Host buffers should be
+ * pinned for the copies to overlap; they must stay valid until the stream reaches this call. */
+int b2r_integrate_host(b2r_ctx* ctx, const b2r_volume* vol, const void* h_depth, int depth_dtype,
+                       const uint8_t* h_color, const b2r_intrinsic* K, const double* extrinsic, double depth_scale,
+                       double depth_trunc, unsigned long long* d_updates, void* stream);
+/* O3D UniformTSDFVolume.reset() */
+int b2r_volume_reset(b2r_ctx* ctx, const b2r_volume* vol, void* stream);
+/* Export owned planes in Open3D order [x][y][z] as separate float arrays (tests / persistence);
+ * d_color_out: float32 [R,R,nz,3] in 0..255 scale or NULL. */
+int b2r_volume_export(b2r_ctx* ctx, const b2r_volume* vol, float* d_tsdf_out, float* d_weight_out,
+                      float* d_color_out, void* stream);
+/* Inverse of b2r_volume_export (load a persisted slab / build test volumes); colour in 0..255 scale. */
+int b2r_volume_import(b2r_ctx* ctx, const b2r_volume* vol, const float* d_tsdf_in, const float* d_weight_in,
+                      const float* d_color_in, void* stream);
+
+/* ---- marching cubes (O3D UniformTSDFVolume.extract_triangle_mesh()) ---------------------- */
+/* Pass 1 (blocking): classify + count + scan.  Halo planes [z_begin-1, z_end] must be valid when the
+ * slab is not the whole cube.  Returns this slab's vertex and triangle counts. */
+int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_vertices, int64_t* n_triangles,
+                           void* stream);
+/* Pass 2a: write vertex positions/colours (double [n_vertices,3]) and this slab's global vertex ids
+ * (vertex_base = number of vertices on lower slabs).  d_vert_id: uint32 [(nz+PAD_LO+PAD_HI)*R*R*... ] is
+ * owned by the context; b2r_mesh_seam_* give access to the seam plane for the NCCL exchange. */
+int b2r_extract_mesh_vertices(b2r_ctx* ctx, const b2r_volume* vol, int64_t vertex_base, double* d_vertices,
+                              double* d_colors, void* stream);
+/* Seam exchange: device pointer + byte size of (a) the first owned plane of the vertex-id table (to
+ * send to the slab below) and (b) the pad plane above the slab (to receive from the slab above). */
+int b2r_mesh_seam_buffers(b2r_ctx* ctx, const b2r_volume* vol, void** d_send_first_plane, void** d_recv_top_plane,
+                          int64_t* bytes);
+/* Pass 2b: write triangles (int32 [n_triangles,3], global vertex ids, winding as Open3D). */
+int b2r_extract_mesh_triangles(b2r_ctx* ctx, const b2r_volume* vol, int32_t* d_triangles, void* stream);
+
+/* ---- O3D UniformTSDFVolume.extract_point_cloud() ------------------------------------------ */
+int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_points, void* stream); /* blocking */
+int b2r_extract_points_emit(b2r_ctx* ctx, const b2r_volume* vol, double* d_points, double* d_normals,
+                            double* d_colors, void* stream);
+
+/* ---- ICP (O3D pipelines.registration.registration_icp, stitcher.py:94-110) ---------------- */
+/* Batched: pair p uses source points [src_off[p], src_off[p+1]) and target points
+ * [tgt_off[p], tgt_off[p+1]) of the concatenated arrays.
+ * estimation: 0 TransformationEstimationPointToPoint, 1 ...PointToPlane, 2 ...ForColoredICP.
+ * criteria = ICPConvergenceCriteria(relative_fitness, relative_rmse, max_iteration). */
+typedef struct b2r_icp_params {
+    double max_correspondence_distance;
+    double relative_fitness, relative_rmse;
+    int32_t max_iteration;
+    int32_t estimation;
+    double lambda_geometric;  /* colored ICP only (0.968) */
+} b2r_icp_params;
+
+typedef struct b2r_icp_result {  /* O3D RegistrationResult */
+    double transformation[16];
+    double fitness;
+    double inlier_rmse;
+    int64_t n_correspondences;
+    int32_t iterations;
+    int32_t converged;
+} b2r_icp_result;
+
+/* Blocking (returns results on the host).  d_corr (optional): int32 [total source points], target
+ * index local to the pair or -1 (RegistrationResult.correspondence_set).
+ * d_src_colors / d_tgt_colors / d_tgt_color_grad are used by estimation 2 only. */
+int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_points, const int64_t* h_src_off,
+                  const double* d_tgt_points, const double* d_tgt_normals, const int64_t* h_tgt_off,
+                  const double* d_src_colors, const double* d_tgt_colors, const double* d_tgt_color_grad,
+                  const double* h_init /* [n_pairs*16] */, const b2r_icp_params* params,
+                  b2r_icp_result* h_results, int32_t* d_corr, void* stream);
+
+/* ---- synthetic frame source (replaces bullet_camera.py:48-85 / data_recorder.py:104-121) -- */
+typedef struct b2r_scene {
+    float c2w[12];            /* camera->world 3x4 row-major */
+    float fx, fy, cx, cy;
+    int32_t W, H;
+    float ell_c[3], ell_r[3]; /* ellipsoid (ell_r[0] <= 0: none) */
+    float plane_z;
+    int32_t has_plane;
+    float checker;
+    float depth_scale;
+    int32_t n_tris;           /* > 0: mesh mode (d_tris float32 [n_tris,9]) */
+    float mesh_min[3], mesh_max[3];
+} b2r_scene;
+int b2r_raycast_scene(b2r_ctx* ctx, const b2r_scene* scene, const float* d_tris, uint16_t* d_depth,
+                      uint8_t* d_color, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RECON_H */

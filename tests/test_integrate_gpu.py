@@ -1,0 +1,145 @@
+"""Parity of the CUDA TSDF integration (through the C ABI) with the CPU oracle.
+Bar: TSDF |delta| <= 1e-5 and weights bit-exact -- the kernel replays Open3D's
+float32 operation order, so the test demands bit-exact TSDF as well."""
+import numpy as np
+import pytest
+
+import helpers as hp
+from b200recon import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_pair(o3d, orc, R, L, trunc, frames, K, color_type=1, z_ranges=None, origin=None, via_host=False):
+    origin = syn.volume_origin(L) if origin is None else origin
+    kt = hp.kt(K)
+    ref = orc.UniformTSDFVolume(L, R, trunc, color_type, origin)
+    intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], *kt)
+    ct = o3d.pipelines.integration.TSDFVolumeColorType(color_type)
+    z_ranges = z_ranges or [(0, R)]
+    vols = [o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, ct, origin, z_range=zr) for zr in z_ranges]
+    for v in vols:
+        v.count_updates = True
+    n_ref = 0
+    for d16, rgb, ext in frames:
+        df = orc.depth_to_float(d16)
+        col = None
+        if color_type == 1:
+            col = rgb
+        elif color_type == 2:
+            col = (rgb.astype(np.float32).mean(2) / 255.0).astype(np.float32)
+        n_ref += ref.integrate(df, col, kt, ext)
+        for v in vols:
+            if via_host:
+                v.integrate_host(d16, rgb if color_type == 1 else None, intr, ext)
+            else:
+                rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(
+                    o3d.geometry.Image(col if col is not None else rgb), o3d.geometry.Image(d16),
+                    depth_scale=1000.0, depth_trunc=3.0, convert_rgb_to_intensity=False)
+                v.integrate(rgbd, intr, ext)
+    return ref, vols, n_ref
+
+
+def _compare(ref, vols, n_ref, color_type, color_tol=1.5):
+    t_ref, w_ref, c_ref = ref.tsdf(), ref.weight(), ref.color()
+    n_gpu = 0
+    for v in vols:
+        ts, w, col = v.export_arrays()
+        zb, ze = v.z_begin, v.z_end
+        assert np.array_equal(w, w_ref[:, :, zb:ze]), "weights must be bit-exact"
+        assert np.array_equal(ts.view(np.uint32), t_ref[:, :, zb:ze].view(np.uint32)), "tsdf must be bit-exact"
+        assert np.abs(ts - t_ref[:, :, zb:ze]).max() <= 1e-5
+        if color_type == 1:
+            m = w > 0
+            err = np.abs(col - c_ref[:, :, zb:ze])[m]
+            assert err.max() <= color_tol, err.max()  # packed 10:10:10 running mean vs float64
+        elif color_type == 2:
+            m = w > 0
+            assert np.abs(col[..., 0] - c_ref[:, :, zb:ze, 0])[m].max() <= 1e-5
+        n_gpu += v.updates()
+    assert n_gpu == n_ref
+    assert n_ref > 0
+
+
+@pytest.mark.parametrize("R,L,trunc", [(64, 0.384, 0.024), (96, 0.384, 0.016), (128, 0.512, 0.012)])
+def test_integrate_bit_exact(o3d, orc, R, L, trunc):
+    K = hp.small_intrinsic(320, 240)
+    frames = hp.make_frames(6, K)
+    ref, vols, n = _run_pair(o3d, orc, R, L, trunc, frames, K)
+    _compare(ref, vols, n, 1)
+
+
+def test_integrate_full_res_frames_host_path(o3d, orc):
+    """640x480 D435 frames through the end-to-end HOST entry point (uint16 depth, H2D inside)."""
+    frames = hp.make_frames(4)
+    ref, vols, n = _run_pair(o3d, orc, 128, 0.512, 0.012, frames, hp.K640, via_host=True)
+    _compare(ref, vols, n, 1)
+
+
+def test_integrate_odd_resolution_scalar_path(o3d, orc):
+    K = hp.small_intrinsic(160, 120)
+    frames = hp.make_frames(3, K)
+    ref, vols, n = _run_pair(o3d, orc, 67, 0.402, 0.02, frames, K)
+    _compare(ref, vols, n, 1)
+
+
+@pytest.mark.parametrize("color_type", [0, 2])
+def test_integrate_color_types(o3d, orc, color_type):
+    K = hp.small_intrinsic(160, 120)
+    frames = hp.make_frames(3, K)
+    ref, vols, n = _run_pair(o3d, orc, 64, 0.384, 0.024, frames, K, color_type=color_type)
+    _compare(ref, vols, n, color_type)
+
+
+def test_integrate_z_slabs_match_whole(o3d, orc):
+    """z-slab sharding: every slab replays the float32 chain from z=0, so the union of the
+    slabs is bit-identical to the single volume."""
+    K = hp.small_intrinsic(320, 240)
+    frames = hp.make_frames(4, K)
+    ref, vols, n = _run_pair(o3d, orc, 96, 0.384, 0.016, frames, K, z_ranges=[(0, 24), (24, 48), (48, 72), (72, 96)])
+    _compare(ref, vols, n, 1)
+    ref, vols, n = _run_pair(o3d, orc, 96, 0.384, 0.016, frames, K, z_ranges=[(0, 37), (37, 96)])
+    _compare(ref, vols, n, 1)
+
+
+def test_integrate_camera_inside_and_behind(o3d, orc):
+    """Camera inside the volume with half of the voxels behind it, tilted view, holes in the depth."""
+    K = hp.small_intrinsic(160, 120)
+    frames = hp.make_frames(5, K, radius=0.12, elevation=55.0)
+    for d16, _, _ in frames:
+        d16[::7, ::5] = 0          # invalid pixels
+        d16[10:20, 30:60] = 40000  # beyond depth_trunc -> 0
+    ref, vols, n = _run_pair(o3d, orc, 80, 0.64, 0.03, frames, K)
+    _compare(ref, vols, n, 1)
+
+
+def test_integrate_many_frames_color_drift(o3d, orc):
+    K = hp.small_intrinsic(160, 120)
+    frames = hp.make_frames(40, K)
+    ref, vols, n = _run_pair(o3d, orc, 64, 0.384, 0.024, frames, K)
+    _compare(ref, vols, n, 1, color_tol=3.0)
+
+
+def test_integrate_errors(o3d):
+    intr = o3d.camera.PinholeCameraIntrinsic(160, 120, 150.0, 150.0, 80.0, 60.0)
+    vol = o3d.pipelines.integration.UniformTSDFVolume(0.4, 32, 0.02, o3d.pipelines.integration.TSDFVolumeColorType.RGB8)
+    d = np.zeros((100, 160), np.uint16)
+    c = np.zeros((100, 160, 3), np.uint8)
+    rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(c), o3d.geometry.Image(d),
+                                                              convert_rgb_to_intensity=False)
+    with pytest.raises(RuntimeError):
+        vol.integrate(rgbd, intr, np.eye(4))          # size mismatch with the intrinsic
+    with pytest.raises(RuntimeError):
+        o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(np.zeros((50, 160, 3), np.uint8)),
+                                                           o3d.geometry.Image(d))
+    # empty frame: nothing updated, nothing crashes
+    d2 = np.zeros((120, 160), np.uint16)
+    c2 = np.zeros((120, 160, 3), np.uint8)
+    rgbd2 = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(c2), o3d.geometry.Image(d2),
+                                                               convert_rgb_to_intensity=False)
+    vol.count_updates = True
+    vol.integrate(rgbd2, intr, np.eye(4))
+    assert vol.updates() == 0
+    ts, w, _ = vol.export_arrays()
+    assert not w.any() and not ts.any()
+    vol.reset()
