@@ -87,3 +87,94 @@ def compute_fpfh_feature(input, search_param):
     f = Feature()
     f.data = np.zeros((33, len(input)), np.float64)
     return f
+
+
+def _check_icp_args(target, max_correspondence_distance, estimation_method):
+    if max_correspondence_distance <= 0.0:
+        raise RuntimeError("Invalid max_correspondence_distance.")
+    kind = estimation_method._kind
+    if kind in (1, 2) and not target.has_normals():
+        raise RuntimeError("TransformationEstimationPointToPlane and TransformationEstimationColoredICP require "
+                           "pre-computed normal vectors for target PointCloud.")
+    if kind == 2:
+        raise NotImplementedError("registration_colored_icp (SURVEY.md 8(f) row f3) is not built yet")
+    return kind
+
+
+def registration_icp_batch(sources, targets, max_correspondence_distance, inits=None,
+                           estimation_method=None, criteria=None, with_correspondences=True, device=None):
+    """Batched Open3D `registration_icp`: pair p registers sources[p] to targets[p]; all pairs run
+    concurrently in ONE sequence of kernel launches (BASELINE config 4).  Returns a list of
+    RegistrationResult.  Multi-GPU: callers give each rank the pairs p with p % world == rank
+    (`parallel.icp_round_robin`); no collective is involved."""
+    estimation_method = estimation_method or TransformationEstimationPointToPoint()
+    criteria = criteria or ICPConvergenceCriteria()
+    n = len(sources)
+    if len(targets) != n:
+        raise RuntimeError("registration_icp_batch: %d sources but %d targets" % (n, len(targets)))
+    kind = -1
+    for tg in targets:
+        kind = _check_icp_args(tg, float(max_correspondence_distance), estimation_method)
+    if n == 0:
+        return []
+    c = runtime.ctx(device)
+    t = runtime.torch()
+    src_off = np.zeros(n + 1, np.int64)
+    tgt_off = np.zeros(n + 1, np.int64)
+    for p in range(n):
+        src_off[p + 1] = src_off[p] + len(sources[p])
+        tgt_off[p + 1] = tgt_off[p] + len(targets[p])
+
+    def cat(arrs):
+        arrs = [a for a in arrs if a.shape[0] > 0]
+        if not arrs:
+            return t.zeros((0, 3), dtype=t.float64, device=c.tdev)
+        return arrs[0] if len(arrs) == 1 else t.cat(arrs)
+
+    S = cat([s._p.get_dev() for s in sources]).contiguous()
+    T = cat([g._p.get_dev() for g in targets]).contiguous()
+    N = cat([g._n.get_dev() for g in targets]).contiguous() if kind == 1 else None
+    init = np.ascontiguousarray(np.stack([np.eye(4) if inits is None or inits[p] is None else
+                                          np.asarray(inits[p], np.float64).reshape(4, 4) for p in range(n)]))
+    prm = _lib.IcpParams(float(max_correspondence_distance), criteria.relative_fitness, criteria.relative_rmse,
+                         criteria.max_iteration, kind, 0.968)
+    res = (_lib.IcpResult * n)()
+    corr = t.empty((int(src_off[n]),), dtype=t.int32, device=c.tdev) if with_correspondences else None
+    _lib.check(_lib.load().b2r_icp_batch(c.handle, n, runtime.ptr(S), src_off.ctypes.data_as(_lib.c_i64p),
+                                         runtime.ptr(T), runtime.ptr(N), tgt_off.ctypes.data_as(_lib.c_i64p),
+                                         None, None, None, init.ctypes.data_as(_lib.c_dp), C.byref(prm), res,
+                                         runtime.ptr(corr), c.stream()))
+    corr_h = corr.cpu().numpy() if corr is not None else None
+    out = []
+    for p in range(n):
+        r = RegistrationResult()
+        r.transformation = np.array(res[p].transformation[:], np.float64).reshape(4, 4)
+        r.fitness = float(res[p].fitness)
+        r.inlier_rmse = float(res[p].inlier_rmse)
+        r.iterations = int(res[p].iterations)
+        r.converged = bool(res[p].converged)
+        if corr_h is not None:
+            cp = corr_h[src_off[p]:src_off[p + 1]]
+            i = np.nonzero(cp >= 0)[0]
+            r.correspondence_set = Vector2iVector(np.stack([i, cp[i]], 1).astype(np.int32))
+        out.append(r)
+    return out
+
+
+def registration_icp(source, target, max_correspondence_distance, init=None, estimation_method=None, criteria=None):
+    """Open3D pipelines.registration.registration_icp (stitcher.py:106-110) -> RegistrationResult
+    with .transformation / .fitness / .inlier_rmse / .correspondence_set."""
+    return registration_icp_batch([source], [target], max_correspondence_distance, [init], estimation_method,
+                                  criteria)[0]
+
+
+def evaluate_registration(source, target, max_correspondence_distance, transformation=None):
+    """Open3D evaluate_registration: correspondences/fitness/rmse at a fixed transformation (zero iterations)."""
+    return registration_icp_batch([source], [target], max_correspondence_distance, [transformation],
+                                  TransformationEstimationPointToPoint(), ICPConvergenceCriteria(max_iteration=0))[0]
+
+
+def registration_colored_icp(source, target, max_correspondence_distance, init=None, estimation_method=None,
+                             criteria=None):
+    """stitcher.py:94-102 -- SURVEY.md 8(f) row f3 ("next"); not built yet, fails loudly."""
+    raise NotImplementedError("registration_colored_icp (SURVEY.md 8(f) row f3) is not built yet")

@@ -1,9 +1,632 @@
-#include "common.cuh"
+// Batched ICP -- replaces Open3D pipelines::registration::RegistrationICP (stitcher.py:94-110; the
+// north_star variant is TransformationEstimationPointToPlane; arithmetic in SURVEY.md A.5).
+//
+// Per pair, once:   voxel-hash of the target (open-addressing table keyed by the 3x21-bit cell
+//                   coordinate, counting sort of the points by cell: count -> scan -> scatter).
+// Per iteration:    ONE kernel.  Each thread transforms its source points by the pair's current T
+//                   (float64), finds the exact nearest target point within the radius (strict
+//                   d^2 < r^2, ties -> lowest target index) by walking the hash cells ring by ring
+//                   with box-distance pruning, and accumulates count, sum d^2 and the 27 normal-equation
+//                   terms (21 upper J^T J + 6 J^T r for point-to-plane; centroid / cross-covariance sums
+//                   for point-to-point) in float64.  Partials are reduced with warp shuffles, one
+//                   shared-memory pass per block and ONE atomic ticket per block; the last block of the
+//                   pair sums the block partials in a fixed order (deterministic), evaluates Open3D's
+//                   convergence test against the previous iteration, solves the 6x6 system (LDL^T with
+//                   diagonal pivoting) or the 3x3 SVD (Umeyama), and composes T <- update * T -- on the
+//                   device, so the max_iteration+1 launches run back to back with no host sync.
+// Pairs are independent (blockIdx.y), so a batch fills the GPU; batches are distributed round-robin
+// over GPUs by the host with no collective.
+#include "frame.cuh"
+#include "scan.cuh"
+
+namespace b2r {
+
+constexpr int ICP_THREADS = 256;
+constexpr int ICP_PTS_PER_THREAD = 4;
+constexpr int ICP_NACC = 29;       // [0] count, [1] sum d^2, [2..28] estimation sums
+constexpr int ICP_MAX_RINGS = 4;   // cell size h >= r / ICP_MAX_RINGS
+constexpr unsigned long long EMPTY_KEY = 0xffffffffffffffffull;
+
+struct IcpPair {
+    long long src_off, n_src, tgt_off, n_tgt, tab_off;
+    unsigned int tab_mask;     // table size - 1 (power of two)
+    int n_blocks;
+    int rings;                 // K = ceil(r / h)
+    double gmin[3];            // grid origin
+    double h, inv_h;
+    double bmin[3], bmax[3];   // target bounding box
+};
+
+struct IcpState {
+    double T[16];
+    double fitness, rmse, prev_fitness, prev_rmse;
+    long long ncorr;
+    int iter;        // number of updates applied so far
+    int done;
+    int converged;
+    unsigned int ticket;
+};
+
+// ---- orderable encoding of doubles for atomicMin/atomicMax ---------------------------------------
+__device__ __forceinline__ long long enc_double(double v) {
+    long long b = __double_as_longlong(v);
+    return b < 0 ? (b ^ 0x7fffffffffffffffll) : b;
+}
+__device__ __forceinline__ double dec_double(long long b) {
+    return __longlong_as_double(b < 0 ? (b ^ 0x7fffffffffffffffll) : b);
+}
+
+__global__ void icp_bbox_init_kernel(long long* __restrict__ bb, int n_pairs) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_pairs * 6) bb[i] = ((i % 6) < 3) ? 0x7fffffffffffffffll : (long long)0x8000000000000000ull;
+}
+
+__global__ void __launch_bounds__(256) icp_bbox_kernel(const double* __restrict__ tgt, const IcpPair* __restrict__ pairs,
+                                                       long long* __restrict__ bb) {
+    const int p = blockIdx.y;
+    const IcpPair P = pairs[p];
+    double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < P.n_tgt; i += (long long)gridDim.x * blockDim.x) {
+        const double* q = tgt + (P.tgt_off + i) * 3;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { mn[k] = fmin(mn[k], q[k]); mx[k] = fmax(mx[k], q[k]); }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], o));
+            mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0 && mn[0] <= mx[0]) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(&bb[p * 6 + k], enc_double(mn[k]));
+            atomicMax(&bb[p * 6 + 3 + k], enc_double(mx[k]));
+        }
+    }
+}
+
+// one thread per pair: choose the cell size from the radius and the point density
+__global__ void icp_setup_kernel(IcpPair* __restrict__ pairs, const long long* __restrict__ bb, int n_pairs, double r) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pairs) return;
+    IcpPair& P = pairs[p];
+    double e[3];
+    for (int k = 0; k < 3; ++k) {
+        P.bmin[k] = P.n_tgt > 0 ? dec_double(bb[p * 6 + k]) : 0.0;
+        P.bmax[k] = P.n_tgt > 0 ? dec_double(bb[p * 6 + 3 + k]) : 0.0;
+        e[k] = P.bmax[k] - P.bmin[k];
+    }
+    // surface-like clouds: mean spacing ~ sqrt(largest bbox face / N)
+    const double a = fmax(e[0] * e[1], fmax(e[1] * e[2], e[0] * e[2]));
+    const double spacing = sqrt(fmax(a, 1e-300) / (double)(P.n_tgt > 0 ? P.n_tgt : 1));
+    double h = fmax(2.5 * spacing, r / (double)ICP_MAX_RINGS);
+    if (h > r) h = r;
+    // keep cell coordinates inside 21 bits
+    const double emax = fmax(e[0], fmax(e[1], e[2])) + 2.0 * (r + h);
+    if (emax / h > 2000000.0) h = emax / 2000000.0;
+    P.h = h;
+    P.inv_h = 1.0 / h;
+    P.rings = (int)ceil(r / h - 1e-12);
+    if (P.rings < 1) P.rings = 1;
+    for (int k = 0; k < 3; ++k) P.gmin[k] = P.bmin[k] - (r + 2.0 * h);
+}
+
+__device__ __forceinline__ unsigned long long cell_key(int ix, int iy, int iz) {
+    return ((unsigned long long)(unsigned)ix << 42) | ((unsigned long long)(unsigned)iy << 21) | (unsigned long long)(unsigned)iz;
+}
+__device__ __forceinline__ unsigned int hash_key(unsigned long long k) {
+    k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+    return (unsigned int)k;
+}
+
+// insert every target point's cell; remember the slot; count points per slot
+__global__ void __launch_bounds__(256) icp_hash_insert_kernel(const double* __restrict__ tgt,
+                                                              const IcpPair* __restrict__ pairs,
+                                                              unsigned long long* __restrict__ keys,
+                                                              uint32_t* __restrict__ counts,
+                                                              uint32_t* __restrict__ slot_of) {
+    const IcpPair P = pairs[blockIdx.y];
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n_tgt) return;
+    const double* q = tgt + (P.tgt_off + i) * 3;
+    const int ix = (int)floor((q[0] - P.gmin[0]) * P.inv_h), iy = (int)floor((q[1] - P.gmin[1]) * P.inv_h),
+              iz = (int)floor((q[2] - P.gmin[2]) * P.inv_h);
+    const unsigned long long key = cell_key(ix, iy, iz);
+    unsigned int s = hash_key(key) & P.tab_mask;
+    while (true) {
+        const unsigned long long prev = atomicCAS(&keys[P.tab_off + s], EMPTY_KEY, key);
+        if (prev == EMPTY_KEY || prev == key) break;
+        s = (s + 1) & P.tab_mask;
+    }
+    atomicAdd(&counts[P.tab_off + s], 1u);
+    slot_of[P.tgt_off + i] = s;
+}
+
+// counting-sort scatter: sorted position = start[slot] + cursor++
+__global__ void __launch_bounds__(256) icp_hash_scatter_kernel(const double* __restrict__ tgt,
+                                                               const double* __restrict__ nrm,
+                                                               const IcpPair* __restrict__ pairs,
+                                                               const uint32_t* __restrict__ starts,
+                                                               uint32_t* __restrict__ cursor,
+                                                               const uint32_t* __restrict__ slot_of,
+                                                               double* __restrict__ s_pts, double* __restrict__ s_nrm,
+                                                               int32_t* __restrict__ s_idx) {
+    const IcpPair P = pairs[blockIdx.y];
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n_tgt) return;
+    const long long g = P.tgt_off + i;
+    const unsigned int s = slot_of[g];
+    const uint32_t pos = starts[P.tab_off + s] + atomicAdd(&cursor[P.tab_off + s], 1u);  // global sorted index
+#pragma unroll
+    for (int k = 0; k < 3; ++k) s_pts[(long long)pos * 3 + k] = tgt[g * 3 + k];
+    if (nrm && s_nrm) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) s_nrm[(long long)pos * 3 + k] = nrm[g * 3 + k];
+    }
+    s_idx[pos] = (int32_t)i;
+}
+
+// ---- small dense solvers (one thread) ---------------------------------------------------------------
+__device__ void ldlt6_solve(const double* Ain, const double* b, double* x) {
+    double A[36];
+    int perm[6];
+    for (int i = 0; i < 36; ++i) A[i] = Ain[i];
+    for (int i = 0; i < 6; ++i) perm[i] = i;
+    for (int k = 0; k < 6; ++k) {
+        int p = k;
+        double best = fabs(A[k * 6 + k]);
+        for (int i = k + 1; i < 6; ++i)
+            if (fabs(A[i * 6 + i]) > best) { best = fabs(A[i * 6 + i]); p = i; }
+        if (p != k) {
+            for (int j = 0; j < 6; ++j) { const double t = A[k * 6 + j]; A[k * 6 + j] = A[p * 6 + j]; A[p * 6 + j] = t; }
+            for (int j = 0; j < 6; ++j) { const double t = A[j * 6 + k]; A[j * 6 + k] = A[j * 6 + p]; A[j * 6 + p] = t; }
+            const int t = perm[k]; perm[k] = perm[p]; perm[p] = t;
+        }
+        const double d = A[k * 6 + k];
+        if (d == 0.0) continue;
+        for (int i = k + 1; i < 6; ++i) {
+            const double l = A[i * 6 + k] / d;
+            for (int j = k + 1; j < 6; ++j) A[i * 6 + j] -= l * A[k * 6 + j];
+            A[i * 6 + k] = l;
+        }
+    }
+    double y[6], z[6];
+    for (int i = 0; i < 6; ++i) {
+        double s = b[perm[i]];
+        for (int j = 0; j < i; ++j) s -= A[i * 6 + j] * y[j];
+        y[i] = s;
+    }
+    for (int i = 0; i < 6; ++i) y[i] = (A[i * 6 + i] != 0.0) ? y[i] / A[i * 6 + i] : 0.0;
+    for (int i = 5; i >= 0; --i) {
+        double s = y[i];
+        for (int j = i + 1; j < 6; ++j) s -= A[j * 6 + i] * z[j];
+        z[i] = s;
+    }
+    for (int i = 0; i < 6; ++i) x[perm[i]] = z[i];
+}
+
+// TransformVector6dToMatrix4d: R = Rz(x2) Ry(x1) Rx(x0), t = x[3:6]
+__device__ void vec6_to_mat4(const double* x, double* T) {
+    const double ca = cos(x[0]), sa = sin(x[0]), cb = cos(x[1]), sb = sin(x[1]), cg = cos(x[2]), sg = sin(x[2]);
+    T[0] = cg * cb; T[1] = cg * sb * sa - sg * ca; T[2] = cg * sb * ca + sg * sa; T[3] = x[3];
+    T[4] = sg * cb; T[5] = sg * sb * sa + cg * ca; T[6] = sg * sb * ca - cg * sa; T[7] = x[4];
+    T[8] = -sb;     T[9] = cb * sa;                T[10] = cb * ca;               T[11] = x[5];
+    T[12] = 0; T[13] = 0; T[14] = 0; T[15] = 1;
+}
+
+__device__ double det3(const double* M) {
+    return M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) + M[2] * (M[3] * M[7] - M[4] * M[6]);
+}
+
+// Rotation of Umeyama's method from the 3x3 cross-covariance S (dst * src^T):  R = U diag(1,1,s) V^T.
+// One-sided Jacobi SVD.
+__device__ void umeyama_rotation(const double* Sin, double* Rm) {
+    double A[9], V[9];
+    for (int i = 0; i < 9; ++i) { A[i] = Sin[i]; V[i] = (i % 4 == 0) ? 1.0 : 0.0; }
+    for (int sweep = 0; sweep < 60; ++sweep) {
+        double off = 0.0;
+        for (int p = 0; p < 2; ++p)
+            for (int q = p + 1; q < 3; ++q) {
+                double al = 0, be = 0, ga = 0;
+                for (int i = 0; i < 3; ++i) { al += A[i * 3 + p] * A[i * 3 + p]; be += A[i * 3 + q] * A[i * 3 + q]; ga += A[i * 3 + p] * A[i * 3 + q]; }
+                off = fmax(off, fabs(ga) / sqrt(fmax(al * be, 1e-300)));
+                if (ga == 0.0) continue;
+                const double zeta = (be - al) / (2.0 * ga);
+                const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                const double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
+                for (int i = 0; i < 3; ++i) {
+                    const double ap = A[i * 3 + p], aq = A[i * 3 + q];
+                    A[i * 3 + p] = c * ap - s * aq; A[i * 3 + q] = s * ap + c * aq;
+                    const double vp = V[i * 3 + p], vq = V[i * 3 + q];
+                    V[i * 3 + p] = c * vp - s * vq; V[i * 3 + q] = s * vp + c * vq;
+                }
+            }
+        if (off < 1e-15) break;
+    }
+    double S[3];
+    for (int j = 0; j < 3; ++j) { double n = 0; for (int i = 0; i < 3; ++i) n += A[i * 3 + j] * A[i * 3 + j]; S[j] = sqrt(n); }
+    int o0 = 0, o1 = 1, o2 = 2;  // sort singular values descending
+    if (S[o0] < S[o1]) { const int t = o0; o0 = o1; o1 = t; }
+    if (S[o1] < S[o2]) { const int t = o1; o1 = o2; o2 = t; }
+    if (S[o0] < S[o1]) { const int t = o0; o0 = o1; o1 = t; }
+    const int ord[3] = {o0, o1, o2};
+    double U[9], Vs[9], Ss[3];
+    for (int j = 0; j < 3; ++j) {
+        Ss[j] = S[ord[j]];
+        for (int i = 0; i < 3; ++i) { U[i * 3 + j] = Ss[j] > 1e-300 ? A[i * 3 + ord[j]] / Ss[j] : 0.0; Vs[i * 3 + j] = V[i * 3 + ord[j]]; }
+    }
+    if (Ss[0] <= 1e-300) { for (int i = 0; i < 9; ++i) Rm[i] = (i % 4 == 0) ? 1.0 : 0.0; return; }
+    const double tiny = 1e-12 * Ss[0];
+    if (Ss[1] <= tiny) {
+        const double u0[3] = {U[0], U[3], U[6]};
+        int k = 0;
+        for (int i = 1; i < 3; ++i) if (fabs(u0[i]) < fabs(u0[k])) k = i;
+        double e[3] = {0, 0, 0};
+        e[k] = 1;
+        double u1[3] = {u0[1] * e[2] - u0[2] * e[1], u0[2] * e[0] - u0[0] * e[2], u0[0] * e[1] - u0[1] * e[0]};
+        const double n = sqrt(u1[0] * u1[0] + u1[1] * u1[1] + u1[2] * u1[2]);
+        U[1] = u1[0] / n; U[4] = u1[1] / n; U[7] = u1[2] / n;
+    }
+    if (Ss[2] <= tiny) {
+        const double u0[3] = {U[0], U[3], U[6]}, u1[3] = {U[1], U[4], U[7]};
+        U[2] = u0[1] * u1[2] - u0[2] * u1[1]; U[5] = u0[2] * u1[0] - u0[0] * u1[2]; U[8] = u0[0] * u1[1] - u0[1] * u1[0];
+    }
+    const double sg = (det3(U) * det3(Vs) < 0) ? -1.0 : 1.0;
+    for (int a = 0; a < 3; ++a)
+        for (int b = 0; b < 3; ++b)
+            Rm[a * 3 + b] = U[a * 3 + 0] * Vs[b * 3 + 0] + U[a * 3 + 1] * Vs[b * 3 + 1] + sg * U[a * 3 + 2] * Vs[b * 3 + 2];
+}
+
+__device__ void matmul4(const double* A, const double* B, double* C) {
+    double t[16];
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            double s = 0;
+            for (int k = 0; k < 4; ++k) s += A[i * 4 + k] * B[k * 4 + j];
+            t[i * 4 + j] = s;
+        }
+    for (int i = 0; i < 16; ++i) C[i] = t[i];
+}
+
+struct IcpArgs {
+    const double* src;
+    const double* s_pts;
+    const double* s_nrm;
+    const int32_t* s_idx;
+    const unsigned long long* keys;
+    const uint32_t* starts;
+    const uint32_t* counts;
+    const IcpPair* pairs;
+    IcpState* states;
+    double* partials;      // [pair][block][ICP_NACC]
+    long long partial_stride;  // blocks reserved per pair
+    int32_t* corr;         // optional [total source points]
+    double r2;
+    double rel_fitness, rel_rmse;
+    int max_iter;
+    int estimation;
+};
+
+__global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_constant__ IcpArgs A) {
+    const int p = blockIdx.y;
+    IcpState& St = A.states[p];
+    if (St.done) return;
+    const IcpPair P = A.pairs[p];
+    if ((int)blockIdx.x >= P.n_blocks) return;
+    __shared__ double s_acc[ICP_THREADS / 32][ICP_NACC];
+    __shared__ int s_last;
+    double T[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) T[i] = St.T[i];
+
+    double acc[ICP_NACC];
+#pragma unroll
+    for (int i = 0; i < ICP_NACC; ++i) acc[i] = 0.0;
+
+    const long long base = (long long)blockIdx.x * (ICP_THREADS * ICP_PTS_PER_THREAD);
+    for (int it = 0; it < ICP_PTS_PER_THREAD; ++it) {
+        const long long i = base + (long long)it * ICP_THREADS + threadIdx.x;
+        if (i >= P.n_src) break;
+        const double* s = A.src + (P.src_off + i) * 3;
+        const double sx = s[0], sy = s[1], sz = s[2];
+        const double q[3] = {T[0] * sx + T[1] * sy + T[2] * sz + T[3], T[4] * sx + T[5] * sy + T[6] * sz + T[7],
+                             T[8] * sx + T[9] * sy + T[10] * sz + T[11]};
+        double best = A.r2;
+        long long bestpos = -1;
+        int bestj = 0x7fffffff;
+        // reject queries farther than r from the target's bounding box
+        double bd = 0.0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double d = q[k] < P.bmin[k] ? P.bmin[k] - q[k] : (q[k] > P.bmax[k] ? q[k] - P.bmax[k] : 0.0);
+            bd += d * d;
+        }
+        if (bd < A.r2 && P.n_tgt > 0) {
+            const double g[3] = {(q[0] - P.gmin[0]) * P.inv_h, (q[1] - P.gmin[1]) * P.inv_h, (q[2] - P.gmin[2]) * P.inv_h};
+            const int c[3] = {(int)floor(g[0]), (int)floor(g[1]), (int)floor(g[2])};
+            // distance from q to the nearest face of its own cell
+            double face = 1e300;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const double f = g[k] - (double)c[k];
+                face = fmin(face, fmin(f, 1.0 - f));
+            }
+            face *= P.h;
+            for (int ring = 0; ring <= P.rings; ++ring) {
+                if (ring > 0) {
+                    const double lo = (double)(ring - 1) * P.h + face;  // everything in ring >= `ring` is at least this far
+                    if (lo * lo >= best) break;
+                }
+                for (int dz = -ring; dz <= ring; ++dz)
+                    for (int dy = -ring; dy <= ring; ++dy) {
+                        const bool shell_yz = (dz == -ring || dz == ring || dy == -ring || dy == ring);
+                        const int step = (shell_yz || ring == 0) ? 1 : 2 * ring;
+                        for (int dx = -ring; dx <= ring; dx += step) {
+                            const int cx = c[0] + dx, cy = c[1] + dy, cz = c[2] + dz;
+                            if ((cx | cy | cz) < 0) continue;
+                            // box distance pruning
+                            const double lx = P.gmin[0] + (double)cx * P.h, ly = P.gmin[1] + (double)cy * P.h, lz = P.gmin[2] + (double)cz * P.h;
+                            const double ex = q[0] < lx ? lx - q[0] : (q[0] > lx + P.h ? q[0] - (lx + P.h) : 0.0);
+                            const double ey = q[1] < ly ? ly - q[1] : (q[1] > ly + P.h ? q[1] - (ly + P.h) : 0.0);
+                            const double ez = q[2] < lz ? lz - q[2] : (q[2] > lz + P.h ? q[2] - (lz + P.h) : 0.0);
+                            // slack of a few ulps: the cell of a point was computed with rounded arithmetic
+                            if (ex * ex + ey * ey + ez * ez > best * (1.0 + 1e-9) + 1e-24) continue;
+                            const unsigned long long key = cell_key(cx, cy, cz);
+                            unsigned int sl = hash_key(key) & P.tab_mask;
+                            unsigned long long kk;
+                            while ((kk = __ldg(&A.keys[P.tab_off + sl])) != key && kk != EMPTY_KEY) sl = (sl + 1) & P.tab_mask;
+                            if (kk != key) continue;
+                            const uint32_t st = __ldg(&A.starts[P.tab_off + sl]), cn = __ldg(&A.counts[P.tab_off + sl]);
+                            for (uint32_t m = st; m < st + cn; ++m) {
+                                const double tx = __ldg(&A.s_pts[(long long)m * 3]) - q[0];
+                                const double ty = __ldg(&A.s_pts[(long long)m * 3 + 1]) - q[1];
+                                const double tz = __ldg(&A.s_pts[(long long)m * 3 + 2]) - q[2];
+                                const double d2 = tx * tx + ty * ty + tz * tz;
+                                if (d2 < best) { best = d2; bestpos = m; bestj = __ldg(&A.s_idx[m]); }
+                                else if (d2 == best && bestpos >= 0) {
+                                    const int j = __ldg(&A.s_idx[m]);
+                                    if (j < bestj) { bestpos = m; bestj = j; }
+                                }
+                            }
+                        }
+                    }
+            }
+        }
+        if (A.corr) A.corr[P.src_off + i] = bestpos >= 0 ? bestj : -1;
+        if (bestpos < 0) continue;
+        const double tx = A.s_pts[bestpos * 3], ty = A.s_pts[bestpos * 3 + 1], tz = A.s_pts[bestpos * 3 + 2];
+        acc[0] += 1.0;
+        acc[1] += best;
+        if (A.estimation == 1) {
+            const double nx = A.s_nrm[bestpos * 3], ny = A.s_nrm[bestpos * 3 + 1], nz = A.s_nrm[bestpos * 3 + 2];
+            const double r = (q[0] - tx) * nx + (q[1] - ty) * ny + (q[2] - tz) * nz;
+            const double J[6] = {q[1] * nz - q[2] * ny, q[2] * nx - q[0] * nz, q[0] * ny - q[1] * nx, nx, ny, nz};
+            int k = 2;
+#pragma unroll
+            for (int a = 0; a < 6; ++a)
+#pragma unroll
+                for (int b = a; b < 6; ++b) acc[k++] += J[a] * J[b];
+#pragma unroll
+            for (int a = 0; a < 6; ++a) acc[23 + a] += J[a] * r;
+        } else {
+            acc[2] += q[0]; acc[3] += q[1]; acc[4] += q[2];
+            acc[5] += tx; acc[6] += ty; acc[7] += tz;
+            const double t3[3] = {tx, ty, tz};
+#pragma unroll
+            for (int a = 0; a < 3; ++a)
+#pragma unroll
+                for (int b = 0; b < 3; ++b) acc[8 + a * 3 + b] += t3[a] * q[b];
+        }
+    }
+
+    // warp shuffle reduction -> one shared-memory pass -> block partial
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < ICP_NACC; ++i) {
+        double v = acc[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if (lane == 0) s_acc[warp][i] = v;
+    }
+    __syncthreads();
+    double* mypart = A.partials + ((long long)p * A.partial_stride + blockIdx.x) * ICP_NACC;
+    if (threadIdx.x < ICP_NACC) {
+        double v = 0.0;
+        for (int w = 0; w < ICP_THREADS / 32; ++w) v += s_acc[w][threadIdx.x];
+        mypart[threadIdx.x] = v;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int t = atomicAdd(&St.ticket, 1u);   // the single atomic of this block
+        s_last = (t == (unsigned int)P.n_blocks - 1u);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+    // ---- last block of the pair: fixed-order sum, convergence test, solve, compose ------------------
+    __shared__ double s_sum[ICP_NACC];
+    if (threadIdx.x < ICP_NACC) {
+        double v = 0.0;
+        const double* base_p = A.partials + (long long)p * A.partial_stride * ICP_NACC + threadIdx.x;
+        for (int b = 0; b < P.n_blocks; ++b) v += __ldcg(base_p + (long long)b * ICP_NACC);
+        s_sum[threadIdx.x] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    St.ticket = 0;
+    const double K = s_sum[0];
+    const double fitness = (K > 0 && P.n_src > 0) ? K / (double)P.n_src : 0.0;
+    const double rmse = K > 0 ? sqrt(s_sum[1] / K) : 0.0;
+    const int n = St.iter;
+    St.prev_fitness = St.fitness; St.prev_rmse = St.rmse;
+    St.fitness = fitness; St.rmse = rmse; St.ncorr = (long long)K;
+    if (n >= 1 && fabs(St.prev_fitness - fitness) < A.rel_fitness && fabs(St.prev_rmse - rmse) < A.rel_rmse) {
+        St.done = 1; St.converged = 1;
+        return;
+    }
+    if (n >= A.max_iter) { St.done = 1; return; }
+    double upd[16];
+    for (int i = 0; i < 16; ++i) upd[i] = (i % 5 == 0) ? 1.0 : 0.0;
+    if (K > 0) {
+        if (A.estimation == 1) {
+            double JTJ[36], nb[6], x[6];
+            int k = 2;
+            for (int a = 0; a < 6; ++a)
+                for (int b = a; b < 6; ++b) { JTJ[a * 6 + b] = s_sum[k]; JTJ[b * 6 + a] = s_sum[k]; ++k; }
+            for (int a = 0; a < 6; ++a) nb[a] = -s_sum[23 + a];
+            ldlt6_solve(JTJ, nb, x);
+            vec6_to_mat4(x, upd);
+        } else {
+            double ms[3], mt[3], Sg[9], Rm[9];
+            for (int a = 0; a < 3; ++a) { ms[a] = s_sum[2 + a] / K; mt[a] = s_sum[5 + a] / K; }
+            for (int a = 0; a < 3; ++a)
+                for (int b = 0; b < 3; ++b) Sg[a * 3 + b] = s_sum[8 + a * 3 + b] / K - mt[a] * ms[b];
+            umeyama_rotation(Sg, Rm);
+            for (int a = 0; a < 3; ++a) {
+                for (int b = 0; b < 3; ++b) upd[a * 4 + b] = Rm[a * 3 + b];
+                upd[a * 4 + 3] = mt[a] - (Rm[a * 3 + 0] * ms[0] + Rm[a * 3 + 1] * ms[1] + Rm[a * 3 + 2] * ms[2]);
+            }
+        }
+    }
+    double Tn[16];
+    matmul4(upd, St.T, Tn);
+    for (int i = 0; i < 16; ++i) St.T[i] = Tn[i];
+    St.iter = n + 1;
+    __threadfence();
+}
+
+}  // namespace b2r
+
+using namespace b2r;
+
+static unsigned int next_pow2(unsigned long long v) {
+    unsigned int p = 16;
+    while ((unsigned long long)p < v && p < (1u << 30)) p <<= 1;
+    return p;
+}
+
 extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_points, const int64_t* h_src_off,
-                  const double* d_tgt_points, const double* d_tgt_normals, const int64_t* h_tgt_off,
-                  const double* d_src_colors, const double* d_tgt_colors, const double* d_tgt_color_grad,
-                  const double* h_init, const b2r_icp_params* params,
-                  b2r_icp_result* h_results, int32_t* d_corr, void* stream) {
-    b2r::set_error("b2r_icp_batch: not implemented yet");
-    return -99;
+                             const double* d_tgt_points, const double* d_tgt_normals, const int64_t* h_tgt_off,
+                             const double* d_src_colors, const double* d_tgt_colors, const double* d_tgt_color_grad,
+                             const double* h_init, const b2r_icp_params* params, b2r_icp_result* h_results,
+                             int32_t* d_corr, void* stream) {
+    B2R_CHECK(ctx && h_src_off && h_tgt_off && params && h_results, -1, "b2r_icp_batch: NULL argument");
+    B2R_CHECK(n_pairs >= 0, -5, "b2r_icp_batch: negative pair count");
+    // Open3D RegistrationICP: LogError("Invalid max_correspondence_distance.")
+    B2R_CHECK(params->max_correspondence_distance > 0.0, -10, "Invalid max_correspondence_distance.");
+    B2R_CHECK(params->estimation == 0 || params->estimation == 1, -11,
+              "b2r_icp_batch: estimation %d is not implemented (0 point-to-point, 1 point-to-plane)", params->estimation);
+    // Open3D: "TransformationEstimationPointToPlane ... require pre-computed normal vectors for target PointCloud."
+    B2R_CHECK(params->estimation != 1 || d_tgt_normals, -12,
+              "TransformationEstimationPointToPlane and TransformationEstimationColoredICP require pre-computed "
+              "normal vectors for target PointCloud.");
+    if (n_pairs == 0) return 0;
+    B2R_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = S(stream);
+    const long long Ns = h_src_off[n_pairs], Nt = h_tgt_off[n_pairs];
+    B2R_CHECK((Ns == 0 || d_src_points) && (Nt == 0 || d_tgt_points), -1, "b2r_icp_batch: NULL point arrays");
+    B2R_CHECK(Nt < (1ll << 31) && Ns < (1ll << 40), -8, "b2r_icp_batch: too many points");
+
+    // ---- host-side pair table ----
+    std::vector<IcpPair> hp(n_pairs);
+    std::vector<IcpState> hs(n_pairs);
+    long long tab_total = 0;
+    int max_blocks = 1;
+    long long max_nt = 0;
+    for (int p = 0; p < n_pairs; ++p) {
+        IcpPair& P = hp[p];
+        memset(&P, 0, sizeof(P));
+        P.src_off = h_src_off[p]; P.n_src = h_src_off[p + 1] - h_src_off[p];
+        P.tgt_off = h_tgt_off[p]; P.n_tgt = h_tgt_off[p + 1] - h_tgt_off[p];
+        B2R_CHECK(P.n_src >= 0 && P.n_tgt >= 0, -5, "b2r_icp_batch: offsets must be non-decreasing");
+        const unsigned int tsz = next_pow2((unsigned long long)P.n_tgt * 2 + 16);
+        P.tab_off = tab_total; P.tab_mask = tsz - 1;
+        tab_total += tsz;
+        P.n_blocks = (int)((P.n_src + ICP_THREADS * ICP_PTS_PER_THREAD - 1) / (ICP_THREADS * ICP_PTS_PER_THREAD));
+        if (P.n_blocks < 1) P.n_blocks = 1;
+        if (P.n_blocks > max_blocks) max_blocks = P.n_blocks;
+        if (P.n_tgt > max_nt) max_nt = P.n_tgt;
+        IcpState& Sx = hs[p];
+        memset(&Sx, 0, sizeof(Sx));
+        for (int i = 0; i < 16; ++i) Sx.T[i] = h_init ? h_init[p * 16 + i] : ((i % 5 == 0) ? 1.0 : 0.0);
+    }
+    B2R_CHECK(tab_total < (1ll << 32), -8, "b2r_icp_batch: hash tables too large");
+
+    // ---- scratch carving ----
+    auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t sz_pairs = al(sizeof(IcpPair) * n_pairs), sz_states = al(sizeof(IcpState) * n_pairs);
+    const size_t sz_bb = al(sizeof(long long) * 6 * n_pairs);
+    if (ctx->icp_a.ensure(sz_pairs + sz_states + sz_bb)) return -102;
+    IcpPair* d_pairs = (IcpPair*)ctx->icp_a.ptr;
+    IcpState* d_states = (IcpState*)((char*)ctx->icp_a.ptr + sz_pairs);
+    long long* d_bb = (long long*)((char*)ctx->icp_a.ptr + sz_pairs + sz_states);
+    const size_t sz_keys = al(sizeof(unsigned long long) * tab_total), sz_u32 = al(sizeof(uint32_t) * tab_total);
+    if (ctx->icp_b.ensure(sz_keys + 3 * sz_u32)) return -102;
+    unsigned long long* d_keys = (unsigned long long*)ctx->icp_b.ptr;
+    uint32_t* d_counts = (uint32_t*)((char*)ctx->icp_b.ptr + sz_keys);
+    uint32_t* d_starts = (uint32_t*)((char*)ctx->icp_b.ptr + sz_keys + sz_u32);
+    uint32_t* d_cursor = (uint32_t*)((char*)ctx->icp_b.ptr + sz_keys + 2 * sz_u32);
+    const size_t sz_pts = al(sizeof(double) * 3 * (size_t)Nt);
+    if (ctx->icp_c.ensure(2 * sz_pts + al(sizeof(int32_t) * (size_t)Nt) + al(sizeof(uint32_t) * (size_t)Nt))) return -102;
+    double* d_spts = (double*)ctx->icp_c.ptr;
+    double* d_snrm = (double*)((char*)ctx->icp_c.ptr + sz_pts);
+    int32_t* d_sidx = (int32_t*)((char*)ctx->icp_c.ptr + 2 * sz_pts);
+    uint32_t* d_slot = (uint32_t*)((char*)ctx->icp_c.ptr + 2 * sz_pts + al(sizeof(int32_t) * (size_t)Nt));
+    if (ctx->icp_d.ensure(sizeof(double) * ICP_NACC * (size_t)max_blocks * n_pairs)) return -102;
+    double* d_partials = (double*)ctx->icp_d.ptr;
+
+    B2R_CUDA(cudaMemcpyAsync(d_pairs, hp.data(), sizeof(IcpPair) * n_pairs, cudaMemcpyHostToDevice, st));
+    B2R_CUDA(cudaMemcpyAsync(d_states, hs.data(), sizeof(IcpState) * n_pairs, cudaMemcpyHostToDevice, st));
+    // the two host vectors die at return: make sure the copies are done before that (pageable memory
+    // copies are staged synchronously by the runtime, this sync is for clarity)
+    B2R_CUDA(cudaStreamSynchronize(st));
+    B2R_CUDA(cudaMemsetAsync(d_keys, 0xff, sizeof(unsigned long long) * tab_total, st));
+    B2R_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(uint32_t) * tab_total, st));
+    B2R_CUDA(cudaMemsetAsync(d_cursor, 0, sizeof(uint32_t) * tab_total, st));
+
+    // ---- build the target hashes ----
+    icp_bbox_init_kernel<<<cdiv(n_pairs * 6, 128), 128, 0, st>>>(d_bb, n_pairs);
+    B2R_LAUNCH_CHECK(ctx);
+    if (max_nt > 0) {
+        const int bx = (int)std::min<long long>(cdiv(max_nt, 256), 256);
+        icp_bbox_kernel<<<dim3(bx, n_pairs), 256, 0, st>>>(d_tgt_points, d_pairs, d_bb);
+        B2R_LAUNCH_CHECK(ctx);
+    }
+    icp_setup_kernel<<<cdiv(n_pairs, 64), 64, 0, st>>>(d_pairs, d_bb, n_pairs, params->max_correspondence_distance);
+    B2R_LAUNCH_CHECK(ctx);
+    if (max_nt > 0) {
+        dim3 grid(cdiv(max_nt, 256), n_pairs);
+        icp_hash_insert_kernel<<<grid, 256, 0, st>>>(d_tgt_points, d_pairs, d_keys, d_counts, d_slot);
+        B2R_LAUNCH_CHECK(ctx);
+        if (int rc = scan_exclusive_u32(ctx, d_counts, d_starts, tab_total, nullptr, st)) return rc;
+        icp_hash_scatter_kernel<<<grid, 256, 0, st>>>(d_tgt_points, d_tgt_normals, d_pairs, d_starts, d_cursor, d_slot,
+                                                      d_spts, d_snrm, d_sidx);
+        B2R_LAUNCH_CHECK(ctx);
+    }
+
+    // ---- iterate: max_iteration + 1 evaluations, no host sync in between ----
+    IcpArgs A;
+    A.src = d_src_points; A.s_pts = d_spts; A.s_nrm = d_snrm; A.s_idx = d_sidx; A.keys = d_keys; A.starts = d_starts;
+    A.counts = d_counts; A.pairs = d_pairs; A.states = d_states; A.partials = d_partials; A.partial_stride = max_blocks;
+    A.corr = d_corr; A.r2 = params->max_correspondence_distance * params->max_correspondence_distance;
+    A.rel_fitness = params->relative_fitness; A.rel_rmse = params->relative_rmse;
+    A.max_iter = params->max_iteration < 0 ? 0 : params->max_iteration; A.estimation = params->estimation;
+    for (int it = 0; it <= A.max_iter; ++it) {
+        icp_iterate_kernel<<<dim3(max_blocks, n_pairs), ICP_THREADS, 0, st>>>(A);
+        B2R_LAUNCH_CHECK(ctx);
+    }
+    B2R_CUDA(cudaMemcpyAsync(hs.data(), d_states, sizeof(IcpState) * n_pairs, cudaMemcpyDeviceToHost, st));
+    B2R_CUDA(cudaStreamSynchronize(st));
+    for (int p = 0; p < n_pairs; ++p) {
+        b2r_icp_result& Rr = h_results[p];
+        for (int i = 0; i < 16; ++i) Rr.transformation[i] = hs[p].T[i];
+        Rr.fitness = hs[p].fitness; Rr.inlier_rmse = hs[p].rmse; Rr.n_correspondences = hs[p].ncorr;
+        Rr.iterations = hs[p].iter; Rr.converged = hs[p].converged;
+    }
+    return 0;
 }
