@@ -45,6 +45,7 @@ struct IcpState {
     int done;
     int converged;
     unsigned int ticket;
+    double dbg[ICP_NACC + 6];
 };
 
 // ---- orderable encoding of doubles for atomicMin/atomicMax ---------------------------------------
@@ -170,42 +171,86 @@ __global__ void __launch_bounds__(256) icp_hash_scatter_kernel(const double* __r
 }
 
 // ---- small dense solvers (one thread) ---------------------------------------------------------------
-__device__ void ldlt6_solve(const double* Ain, const double* b, double* x) {
-    double A[36];
-    int perm[6];
-    for (int i = 0; i < 36; ++i) A[i] = Ain[i];
-    for (int i = 0; i < 6; ++i) perm[i] = i;
-    for (int k = 0; k < 6; ++k) {
-        int p = k;
-        double best = fabs(A[k * 6 + k]);
-        for (int i = k + 1; i < 6; ++i)
-            if (fabs(A[i * 6 + i]) > best) { best = fabs(A[i * 6 + i]); p = i; }
-        if (p != k) {
-            for (int j = 0; j < 6; ++j) { const double t = A[k * 6 + j]; A[k * 6 + j] = A[p * 6 + j]; A[p * 6 + j] = t; }
-            for (int j = 0; j < 6; ++j) { const double t = A[j * 6 + k]; A[j * 6 + k] = A[j * 6 + p]; A[j * 6 + p] = t; }
-            const int t = perm[k]; perm[k] = perm[p]; perm[p] = t;
+// Symmetric 6x6 solve, LDL^T with diagonal pivoting (largest remaining diagonal first, like Eigen's
+// LDLT that Open3D's SolveJacobianSystemAndObtainExtrinsicMatrix calls).  Straight-line code: every
+// array index is a compile-time constant after unrolling (the pivot swap is a chain of predicated
+// exchanges), so the whole system lives in registers.
+template <int K, int I>
+__device__ __forceinline__ void ldlt6_swap(double (&A)[6][6], double (&b)[6], int (&perm)[6]) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) { const double t = A[K][j]; A[K][j] = A[I][j]; A[I][j] = t; }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) { const double t = A[j][K]; A[j][K] = A[j][I]; A[j][I] = t; }
+    { const double t = b[K]; b[K] = b[I]; b[I] = t; }
+    { const int t = perm[K]; perm[K] = perm[I]; perm[I] = t; }
+}
+
+template <int K>
+__device__ __forceinline__ void ldlt6_step(double (&A)[6][6], double (&b)[6], int (&perm)[6]) {
+    int p = K;
+    double best = fabs(A[K][K]);
+#pragma unroll
+    for (int i = K + 1; i < 6; ++i)
+        if (fabs(A[i][i]) > best) { best = fabs(A[i][i]); p = i; }
+    if (K + 1 < 6 && p == K + 1) ldlt6_swap<K, (K + 1 < 6 ? K + 1 : K)>(A, b, perm);
+    if (K + 2 < 6 && p == K + 2) ldlt6_swap<K, (K + 2 < 6 ? K + 2 : K)>(A, b, perm);
+    if (K + 3 < 6 && p == K + 3) ldlt6_swap<K, (K + 3 < 6 ? K + 3 : K)>(A, b, perm);
+    if (K + 4 < 6 && p == K + 4) ldlt6_swap<K, (K + 4 < 6 ? K + 4 : K)>(A, b, perm);
+    if (K + 5 < 6 && p == K + 5) ldlt6_swap<K, (K + 5 < 6 ? K + 5 : K)>(A, b, perm);
+    const double d = A[K][K];
+    if (d != 0.0) {
+#pragma unroll
+        for (int i = K + 1; i < 6; ++i) {
+            const double l = A[i][K] / d;
+#pragma unroll
+            for (int j = K + 1; j < 6; ++j) A[i][j] -= l * A[K][j];
+            A[i][K] = l;
         }
-        const double d = A[k * 6 + k];
-        if (d == 0.0) continue;
-        for (int i = k + 1; i < 6; ++i) {
-            const double l = A[i * 6 + k] / d;
-            for (int j = k + 1; j < 6; ++j) A[i * 6 + j] -= l * A[k * 6 + j];
-            A[i * 6 + k] = l;
-        }
+    } else {
+#pragma unroll
+        for (int i = K + 1; i < 6; ++i) A[i][K] = 0.0;
     }
-    double y[6], z[6];
+}
+
+__device__ void ldlt6_solve(const double* Ain, const double* bin, double* x) {
+    double A[6][6], b[6];
+    int perm[6];
+#pragma unroll
     for (int i = 0; i < 6; ++i) {
-        double s = b[perm[i]];
-        for (int j = 0; j < i; ++j) s -= A[i * 6 + j] * y[j];
+        perm[i] = i;
+        b[i] = bin[i];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) A[i][j] = Ain[i * 6 + j];
+    }
+    ldlt6_step<0>(A, b, perm);
+    ldlt6_step<1>(A, b, perm);
+    ldlt6_step<2>(A, b, perm);
+    ldlt6_step<3>(A, b, perm);
+    ldlt6_step<4>(A, b, perm);
+    ldlt6_step<5>(A, b, perm);
+    double y[6], z[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {   // L y = P b
+        double s = b[i];
+#pragma unroll
+        for (int j = 0; j < i; ++j) s -= A[i][j] * y[j];
         y[i] = s;
     }
-    for (int i = 0; i < 6; ++i) y[i] = (A[i * 6 + i] != 0.0) ? y[i] / A[i * 6 + i] : 0.0;
-    for (int i = 5; i >= 0; --i) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) y[i] = (A[i][i] != 0.0) ? y[i] / A[i][i] : 0.0;   // D
+#pragma unroll
+    for (int i = 5; i >= 0; --i) {  // L^T z = y
         double s = y[i];
-        for (int j = i + 1; j < 6; ++j) s -= A[j * 6 + i] * z[j];
+#pragma unroll
+        for (int j = i + 1; j < 6; ++j) s -= A[j][i] * z[j];
         z[i] = s;
     }
-    for (int i = 0; i < 6; ++i) x[perm[i]] = z[i];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {   // x = P^T z
+#pragma unroll
+        for (int j = 0; j < 6; ++j)
+            if (perm[i] == j) x[j] = z[i];
+    }
 }
 
 // TransformVector6dToMatrix4d: R = Rz(x2) Ry(x1) Rx(x0), t = x[3:6]
@@ -469,6 +514,7 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_c
         St.done = 1; St.converged = 1;
         return;
     }
+    if (n == 0) for (int i = 0; i < ICP_NACC; ++i) St.dbg[i] = s_sum[i];
     if (n >= A.max_iter) { St.done = 1; return; }
     double upd[16];
     for (int i = 0; i < 16; ++i) upd[i] = (i % 5 == 0) ? 1.0 : 0.0;
@@ -480,6 +526,7 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_c
                 for (int b = a; b < 6; ++b) { JTJ[a * 6 + b] = s_sum[k]; JTJ[b * 6 + a] = s_sum[k]; ++k; }
             for (int a = 0; a < 6; ++a) nb[a] = -s_sum[23 + a];
             ldlt6_solve(JTJ, nb, x);
+            if (n == 0) for (int i = 0; i < 6; ++i) St.dbg[ICP_NACC + i] = x[i];
             vec6_to_mat4(x, upd);
         } else {
             double ms[3], mt[3], Sg[9], Rm[9];
@@ -622,6 +669,7 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
     }
     B2R_CUDA(cudaMemcpyAsync(hs.data(), d_states, sizeof(IcpState) * n_pairs, cudaMemcpyDeviceToHost, st));
     B2R_CUDA(cudaStreamSynchronize(st));
+    if (getenv("B2R_ICP_DEBUG")) for (int i = 0; i < ICP_NACC + 6; ++i) fprintf(stderr, "dbg[%d]=%.17g\n", i, hs[0].dbg[i]);
     for (int p = 0; p < n_pairs; ++p) {
         b2r_icp_result& Rr = h_results[p];
         for (int i = 0; i < 16; ++i) Rr.transformation[i] = hs[p].T[i];
