@@ -25,12 +25,13 @@ __global__ void depth_to_float_kernel(const void* __restrict__ depth, int dtype,
 
 // One pass per frame: metres depth (optionally converting from the raw dtype), the
 // depth->camera-distance multiplier of O3D CreateDepthToCameraDistanceMultiplierFloatImage
-// (float32, sqrtf(xx^2 + yy^2 + 1), same operation order) interleaved as float2 so the integrate
-// kernel fetches both with one 8-byte gather; colour packed to one 32-bit word per pixel.
+// (float32, sqrtf(xx^2 + yy^2 + 1), same operation order) and the colour packed to one 32-bit word,
+// interleaved as one 16-byte pixel record {depth, multiplier, colour bits, 0} so the integrate kernel
+// fetches everything a voxel needs from the frame with a single 16-byte gather.
 __global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, int convert, float scale, float trunc,
                                      const void* __restrict__ color, int color_mode, int H, int W, float cx, float cy,
-                                     float ffl_inv_x, float ffl_inv_y, float2* __restrict__ dm,
-                                     uint32_t* __restrict__ rgba, unsigned int* __restrict__ dmax_bits) {
+                                     float ffl_inv_x, float ffl_inv_y, float4* __restrict__ px,
+                                     unsigned int* __restrict__ dmax_bits) {
     const int u = blockIdx.x * blockDim.x + threadIdx.x;
     const int v = blockIdx.y;
     float d = 0.0f;
@@ -44,13 +45,14 @@ __global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, 
         const float xx = ((float)u - cx) * ffl_inv_x;
         const float yy = ((float)v - cy) * ffl_inv_y;
         const float m = sqrtf(xx * xx + yy * yy + 1.0f);
-        dm[i] = make_float2(d, m);
+        uint32_t c = 0u;
         if (color_mode == 1) {
             const uint8_t* p = (const uint8_t*)color + i * 3;
-            rgba[i] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+            c = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
         } else if (color_mode == 2) {
-            rgba[i] = __float_as_uint(((const float*)color)[i]);
+            c = __float_as_uint(((const float*)color)[i]);
         }
+        px[i] = make_float4(d, m, __uint_as_float(c), 0.0f);
     }
     // frame-wide maximum depth (positive floats order like their bit patterns)
     float m = (d > 0.0f) ? d : 0.0f;
@@ -63,16 +65,14 @@ int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, dou
                   const void* d_color, int color_mode, const b2r_intrinsic* K, cudaStream_t stream) {
     const int H = K->height, W = K->width;
     const size_t n = (size_t)H * W;
-    if (ctx->frame_dm.ensure(n * sizeof(float2))) return -102;
-    if (ctx->frame_rgba.ensure(n * sizeof(uint32_t))) return -102;
+    if (ctx->frame_dm.ensure(n * sizeof(float4))) return -102;
     unsigned int* dmax = (unsigned int*)ctx->small.ptr + SMALL_DMAX;
     B2R_CUDA(cudaMemsetAsync(dmax, 0, sizeof(unsigned int), stream));
     const float ffl_inv_x = 1.0f / (float)K->fx, ffl_inv_y = 1.0f / (float)K->fy;
     dim3 block(128), grid(cdiv(W, 128), H);
     frame_prepare_kernel<<<grid, block, 0, stream>>>(d_depth, dtype, convert, (float)depth_scale, (float)depth_trunc,
                                                      d_color, color_mode, H, W, (float)K->cx, (float)K->cy, ffl_inv_x,
-                                                     ffl_inv_y, (float2*)ctx->frame_dm.ptr,
-                                                     (uint32_t*)ctx->frame_rgba.ptr, dmax);
+                                                     ffl_inv_y, (float4*)ctx->frame_dm.ptr, dmax);
     B2R_LAUNCH_CHECK(ctx);
     return 0;
 }

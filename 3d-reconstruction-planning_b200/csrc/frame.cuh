@@ -10,7 +10,7 @@ constexpr int SMALL_TOTAL64 = 128;     // uint64 index (byte 1024): scan totals
 constexpr int SMALL_TOTAL64_B = 129;
 constexpr int SMALL_TOTAL64_C = 130;
 
-// Fills ctx->frame_dm (float2 {depth_m, multiplier}) and ctx->frame_rgba for one frame.
+// Fills ctx->frame_dm (float4 {depth_m, multiplier, colour bits, 0} per pixel) for one frame.
 // color_mode: 0 none, 1 uint8 x3, 2 float32 gray.
 int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
                   const void* d_color, int color_mode, const b2r_intrinsic* K, cudaStream_t stream);
