@@ -31,6 +31,7 @@ __global__ void depth_to_float_kernel(const void* __restrict__ depth, int dtype,
 __global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, int convert, float scale, float trunc,
                                      const void* __restrict__ color, int color_mode, int H, int W, float cx, float cy,
                                      float ffl_inv_x, float ffl_inv_y, float4* __restrict__ px,
+                                     const MipDesc M, unsigned int* __restrict__ mip,
                                      unsigned int* __restrict__ dmax_bits) {
     const int u = blockIdx.x * blockDim.x + threadIdx.x;
     const int v = blockIdx.y;
@@ -54,11 +55,39 @@ __global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, 
         }
         px[i] = make_float4(d, m, __uint_as_float(c), 0.0f);
     }
-    // frame-wide maximum depth (positive floats order like their bit patterns)
+    // Max-depth pyramid (cells of 8, 16, 32, 64, 128 pixels; positive floats order like their bit patterns)
+    // and the frame-wide maximum.  The integrate kernel bounds the depth any voxel of a lane's z chunk can
+    // see by the maximum over the <= 2x2 cells covering the chunk's image footprint and skips voxels lying
+    // more than sdf_trunc behind it (hierarchical-z culling).  blockDim.x = 128: a warp is 32 pixels of a row.
     float m = (d > 0.0f) ? d : 0.0f;
+    const int lane = threadIdx.x & 31;
+    const int u0 = u - lane;   // first pixel of this warp (multiple of 32)
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if ((threadIdx.x & 31) == 0 && m > 0.0f) atomicMax(dmax_bits, __float_as_uint(m));
+    for (int o = 1; o < 8; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((lane & 7) == 0 && m > 0.0f) atomicMax(&mip[M.off[0] + (v >> 3) * M.w[0] + (u >> 3)], __float_as_uint(m));
+    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
+    if ((lane & 15) == 0 && m > 0.0f) atomicMax(&mip[M.off[1] + (v >> 4) * M.w[1] + (u >> 4)], __float_as_uint(m));
+    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 16));
+    if (lane == 0 && m > 0.0f) {
+#pragma unroll
+        for (int l = 2; l < B2R_MIP_LEVELS; ++l)
+            atomicMax(&mip[M.off[l] + (v >> (3 + l)) * M.w[l] + (u0 >> (3 + l))], __float_as_uint(m));
+        atomicMax(dmax_bits, __float_as_uint(m));
+    }
+}
+
+MipDesc mip_desc(int H, int W) {
+    MipDesc M;
+    int off = 0;
+    for (int l = 0; l < B2R_MIP_LEVELS; ++l) {
+        const int cell = 8 << l;
+        M.w[l] = (W + cell - 1) / cell;
+        M.h[l] = (H + cell - 1) / cell;
+        M.off[l] = off;
+        off += M.w[l] * M.h[l];
+    }
+    M.total = off;
+    return M;
 }
 
 int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
@@ -66,13 +95,16 @@ int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, dou
     const int H = K->height, W = K->width;
     const size_t n = (size_t)H * W;
     if (ctx->frame_dm.ensure(n * sizeof(float4))) return -102;
-    unsigned int* dmax = (unsigned int*)ctx->small.ptr + SMALL_DMAX;
-    B2R_CUDA(cudaMemsetAsync(dmax, 0, sizeof(unsigned int), stream));
+    const MipDesc M = mip_desc(H, W);
+    if (ctx->frame_mip.ensure((size_t)(M.total + 1) * sizeof(float))) return -102;
+    B2R_CUDA(cudaMemsetAsync(ctx->frame_mip.ptr, 0, (size_t)(M.total + 1) * sizeof(float), stream));
+    unsigned int* mip = (unsigned int*)ctx->frame_mip.ptr;
+    unsigned int* dmax = mip + M.total;   // frame-wide maximum depth sits behind the pyramid
     const float ffl_inv_x = 1.0f / (float)K->fx, ffl_inv_y = 1.0f / (float)K->fy;
     dim3 block(128), grid(cdiv(W, 128), H);
     frame_prepare_kernel<<<grid, block, 0, stream>>>(d_depth, dtype, convert, (float)depth_scale, (float)depth_trunc,
                                                      d_color, color_mode, H, W, (float)K->cx, (float)K->cy, ffl_inv_x,
-                                                     ffl_inv_y, (float4*)ctx->frame_dm.ptr, dmax);
+                                                     ffl_inv_y, (float4*)ctx->frame_dm.ptr, M, mip, dmax);
     B2R_LAUNCH_CHECK(ctx);
     return 0;
 }

@@ -10,7 +10,13 @@ constexpr int SMALL_TOTAL64 = 128;     // uint64 index (byte 1024): scan totals
 constexpr int SMALL_TOTAL64_B = 129;
 constexpr int SMALL_TOTAL64_C = 130;
 
-// Fills ctx->frame_dm (float4 {depth_m, multiplier, colour bits, 0} per pixel) for one frame.
+constexpr int B2R_MIP_LEVELS = 5;   // max-depth pyramid cells: 8, 16, 32, 64, 128 pixels
+struct MipDesc {
+    int w[B2R_MIP_LEVELS], h[B2R_MIP_LEVELS], off[B2R_MIP_LEVELS], total;
+};
+MipDesc mip_desc(int H, int W);
+
+// Fills ctx->frame_mip (max-depth pyramid) and ctx->frame_dm (float4 {depth_m, multiplier, colour bits, 0} per pixel) for one frame.
 // color_mode: 0 none, 1 uint8 x3, 2 float32 gray.
 int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
                   const void* d_color, int color_mode, const b2r_intrinsic* K, cudaStream_t stream);
