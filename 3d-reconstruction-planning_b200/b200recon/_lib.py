@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libb200recon.so")
+LIB_PATH = os.environ.get("B2R_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libb200recon.so")
 
 c_vp = C.c_void_p
 c_dp = C.POINTER(C.c_double)
@@ -62,6 +62,7 @@ SIGNATURES = {
     "b2r_integrate": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, C.POINTER(Intrinsic), c_dp, c_vp, c_vp]),
     "b2r_integrate_host": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, C.c_int, c_vp, C.POINTER(Intrinsic), c_dp,
                                      C.c_double, C.c_double, c_vp, c_vp]),
+    "b2r_selftest_div": (C.c_int, [c_vp, C.c_int64, C.c_uint32, c_i64p, c_vp]),
     "b2r_volume_reset": (C.c_int, [c_vp, C.POINTER(Volume), c_vp]),
     "b2r_volume_export": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, c_vp, c_vp]),
     "b2r_volume_import": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, c_vp, c_vp]),

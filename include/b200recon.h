@@ -96,6 +96,10 @@ int b2r_integrate(b2r_ctx* ctx, const b2r_volume* vol, const float* d_depth, con
 int b2r_integrate_host(b2r_ctx* ctx, const b2r_volume* vol, const void* h_depth, int depth_dtype,
                        const uint8_t* h_color, const b2r_intrinsic* K, const double* extrinsic, double depth_scale,
                        double depth_trunc, unsigned long long* d_updates, void* stream);
+/* Device self-test (blocking): the integrate kernel computes Open3D's IEEE float32 divisions with a shared
+ * refined reciprocal; this runs n pseudo-random cases (projection-like, full-range, running-mean-like and
+ * near-half-way quotients) through that code and through the `/` operator; mismatches[4] = count per family. */
+int b2r_selftest_div(b2r_ctx* ctx, int64_t n, uint32_t seed, int64_t* mismatches, void* stream);
 /* O3D UniformTSDFVolume.reset() */
 int b2r_volume_reset(b2r_ctx* ctx, const b2r_volume* vol, void* stream);
 /* Export owned planes in Open3D order [x][y][z] as separate float arrays (tests / persistence);

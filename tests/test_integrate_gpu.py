@@ -143,3 +143,15 @@ def test_integrate_errors(o3d):
     ts, w, _ = vol.export_arrays()
     assert not w.any() and not ts.any()
     vol.reset()
+
+
+def test_shared_reciprocal_division_is_ieee(o3d):
+    """The kernel's float32 divisions (projection, running mean) share a refined reciprocal; on the device they
+    must equal the `/` operator bit for bit (2^28 pseudo-random cases incl. near-half-way quotients)."""
+    import ctypes as C
+    from b200recon import _lib, runtime
+    c = runtime.ctx()
+    for seed in (1, 12345):
+        bad = (C.c_int64 * 4)(-1, -1, -1, -1)
+        _lib.check(_lib.load().b2r_selftest_div(c.handle, 1 << 28, seed, bad, c.stream()))
+        assert list(bad) == [0, 0, 0, 0], list(bad)
