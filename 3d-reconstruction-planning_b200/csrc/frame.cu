@@ -49,7 +49,9 @@ __global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, 
         uint32_t c = 0u;
         if (color_mode == 1) {
             const uint8_t* p = (const uint8_t*)color + i * 3;
-            c = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+            // the volume's own packed format (10:10:10 fixed point, value * 4) so that the integrate kernel
+            // unpacks frame and voxel colour with the same three instructions
+            c = ((uint32_t)p[0] << 2) | ((uint32_t)p[1] << 12) | ((uint32_t)p[2] << 22);
         } else if (color_mode == 2) {
             c = __float_as_uint(((const float*)color)[i]);
         }
