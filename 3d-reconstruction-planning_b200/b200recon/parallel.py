@@ -1,0 +1,305 @@
+"""Multi-GPU layer: one process per GPU, `torch.distributed` for the plumbing.
+
+  * `SlabVolume`     -- a dense R^3 TSDF cube sharded into z-slabs, one per rank.  Every rank integrates
+                        every frame into its own slab: NO data-path collective during integration (the
+                        float32 z-chain of each slab starts with the replay of the planes below it, so every
+                        slab is bit-identical to the single-GPU volume).
+  * halo exchange    -- before extraction each rank sends its first B2R_PAD_HI owned planes to the rank
+                        below and its last B2R_PAD_LO owned planes to the rank above (the volume is stored
+                        z-slowest, so a plane is one contiguous message -- no pack kernel).
+  * mesh gather      -- per-rank vertex/triangle counts -> all_gather -> global vertex bases; one more
+                        seam message (the vertex-id table of the first owned plane goes to the rank below);
+                        vertices / triangles are sent to rank 0.
+  * `icp_round_robin`-- batched ICP pairs, pair p -> rank p % world, no collective on the data path.
+
+The collectives are written against `torch.distributed` only (NCCL over NVLink on the GPUs; the same code
+runs on the `gloo` backend with CPU tensors, which is how the host logic is tested without a GPU).
+"""
+import numpy as np
+
+from . import _lib
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def world_info(group=None):
+    """(rank, world) of the default (or given) process group; (0, 1) when torch.distributed is not initialised."""
+    dist = _dist()
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(group), dist.get_world_size(group)
+    return 0, 1
+
+
+def slab_range(resolution, rank, world):
+    """Planes [z_begin, z_end) owned by `rank`: contiguous, balanced to within one plane."""
+    R = int(resolution)
+    return R * rank // world, R * (rank + 1) // world
+
+
+def slab_ranges(resolution, world):
+    return [slab_range(resolution, r, world) for r in range(world)]
+
+
+# --------------------------------------------------------------------------------------------------
+# halo exchange
+# --------------------------------------------------------------------------------------------------
+def halo_plan(rank, world, n_owned, pad_lo=_lib.PAD_LO, pad_hi=_lib.PAD_HI):
+    """Messages of one rank as (kind, peer, first_plane, n_planes) in units of planes of the padded slab
+    array (plane p holds z = z_begin - pad_lo + p).  `send_down` = first pad_hi owned planes -> rank-1's top
+    pad; `send_up` = last pad_lo owned planes -> rank+1's bottom pad."""
+    ops = []
+    if n_owned < max(pad_lo, pad_hi) and world > 1:
+        raise RuntimeError("slab of %d planes is thinner than the halo (%d): use fewer ranks" %
+                           (n_owned, max(pad_lo, pad_hi)))
+    if rank > 0:
+        ops.append(("send", rank - 1, pad_lo, pad_hi))                       # my first owned planes go down
+        ops.append(("recv", rank - 1, 0, pad_lo))                            # bottom pad comes from below
+    if rank < world - 1:
+        ops.append(("send", rank + 1, pad_lo + n_owned - pad_lo, pad_lo))    # my last owned planes go up
+        ops.append(("recv", rank + 1, pad_lo + n_owned, pad_hi))             # top pad comes from above
+    return ops
+
+
+def exchange_halos(arrays, n_owned, rank=None, world=None, group=None, pad_lo=_lib.PAD_LO, pad_hi=_lib.PAD_HI):
+    """Fill the halo planes of every array in `arrays` (torch tensors shaped [pad_lo + n_owned + pad_hi, ...],
+    plane-major, contiguous) from the neighbouring ranks.  One batch of point-to-point messages
+    (ncclGroupStart/End under NCCL)."""
+    dist = _dist()
+    if rank is None or world is None:
+        rank, world = world_info(group)
+    if world == 1:
+        return
+    p2p = []
+    for a in arrays:
+        if a is None:
+            continue
+        for kind, peer, first, n in halo_plan(rank, world, n_owned, pad_lo, pad_hi):
+            view = a[first:first + n]
+            gpeer = peer if group is None else dist.get_global_rank(group, peer)
+            p2p.append(dist.P2POp(dist.isend if kind == "send" else dist.irecv, view, gpeer, group))
+    for w in dist.batch_isend_irecv(p2p):
+        w.wait()
+
+
+# --------------------------------------------------------------------------------------------------
+# variable-length gathers
+# --------------------------------------------------------------------------------------------------
+def all_gather_counts(counts, device, group=None):
+    """counts: sequence of python ints of this rank -> int64 array [world, len(counts)] (same on all ranks)."""
+    import torch
+    dist = _dist()
+    rank, world = world_info(group)
+    mine = torch.tensor([int(c) for c in counts], dtype=torch.int64, device=device)
+    if world == 1:
+        return mine.cpu().numpy()[None, :]
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine, group=group)
+    return torch.stack(out).cpu().numpy()
+
+
+def exclusive_bases(per_rank_counts):
+    """Exclusive prefix sum over ranks: base[r] = sum(counts[:r])."""
+    c = np.asarray(per_rank_counts, np.int64)
+    return np.concatenate([[0], np.cumsum(c)[:-1]]).astype(np.int64)
+
+
+def gather_rows(tensor, counts, dst=0, group=None):
+    """Concatenate row blocks of different lengths on rank `dst` (rank order).  `counts[r]` = rows of rank r
+    (from all_gather_counts).  Returns the concatenated tensor on dst, None elsewhere."""
+    import torch
+    dist = _dist()
+    rank, world = world_info(group)
+    if world == 1:
+        return tensor
+    g = (lambda r: r) if group is None else (lambda r: dist.get_global_rank(group, r))
+    if rank == dst:
+        total = int(sum(int(c) for c in counts))
+        out = torch.empty((total,) + tuple(tensor.shape[1:]), dtype=tensor.dtype, device=tensor.device)
+        ops, off = [], 0
+        for r in range(world):
+            n = int(counts[r])
+            if r == dst:
+                out[off:off + n].copy_(tensor)
+            elif n > 0:
+                ops.append(dist.P2POp(dist.irecv, out[off:off + n], g(r), group))
+            off += n
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        return out
+    if int(counts[rank]) > 0:
+        for w in dist.batch_isend_irecv([dist.P2POp(dist.isend, tensor.contiguous(), g(dst), group)]):
+            w.wait()
+    return None
+
+
+# --------------------------------------------------------------------------------------------------
+# the sharded volume
+# --------------------------------------------------------------------------------------------------
+class _RawCuda:
+    """Exposes a raw device pointer as an int32 array to torch (`torch.as_tensor`) without copying."""
+
+    def __init__(self, ptr, n_int32):
+        self.__cuda_array_interface__ = {"shape": (int(n_int32),), "typestr": "<i4", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class SlabVolume:
+    """`UniformTSDFVolume` sharded into z-slabs over the ranks of a process group (BASELINE configs 3 and 5).
+
+        vol = SlabVolume(length, resolution, sdf_trunc, color_type, origin)   # every rank, same arguments
+        vol.integrate(rgbd, intrinsic, extrinsic)                             # every rank, every frame
+        mesh = vol.extract_triangle_mesh()                                    # TriangleMesh on rank 0, None elsewhere
+
+    The mesh is the single-volume mesh: same vertex and triangle sets (vertex ids are global)."""
+
+    def __init__(self, length, resolution, sdf_trunc, color_type=None, origin=(0.0, 0.0, 0.0), group=None, device=None):
+        from .pipelines import integration
+        self.group = group
+        self.rank, self.world = world_info(group)
+        self.resolution = int(resolution)
+        ct = integration.TSDFVolumeColorType.RGB8 if color_type is None else color_type
+        self.z_begin, self.z_end = slab_range(resolution, self.rank, self.world)
+        if self.world > 1 and (self.z_end - self.z_begin) < max(_lib.PAD_LO, _lib.PAD_HI):
+            raise RuntimeError("SlabVolume: %d planes over %d ranks leaves slabs thinner than the halo" %
+                               (self.resolution, self.world))
+        self.local = integration.UniformTSDFVolume(length, resolution, sdf_trunc, ct, origin,
+                                                   z_range=(self.z_begin, self.z_end), device=device)
+        self._halo_valid = False
+
+    # ---- integration: no collective -------------------------------------------------------------
+    def integrate(self, image, intrinsic, extrinsic):
+        self.local.integrate(image, intrinsic, extrinsic)
+        self._halo_valid = False
+
+    def integrate_device(self, depth_f32, color, intrinsic, extrinsic):
+        self.local.integrate_device(depth_f32, color, intrinsic, extrinsic)
+        self._halo_valid = False
+
+    def integrate_host(self, depth, color, intrinsic, extrinsic, depth_scale=1000.0, depth_trunc=3.0):
+        self.local.integrate_host(depth, color, intrinsic, extrinsic, depth_scale, depth_trunc)
+        self._halo_valid = False
+
+    def reset(self):
+        self.local.reset()
+        self._halo_valid = False
+
+    # ---- exchange -------------------------------------------------------------------------------
+    def exchange_halos(self):
+        """One-plane-below / two-planes-above halo of {tsdf, weight} and colour from the neighbour slabs."""
+        if not self._halo_valid:
+            exchange_halos([self.local._tsdfw, self.local._color], self.z_end - self.z_begin, self.rank, self.world,
+                           self.group)
+            self._halo_valid = True
+
+    # ---- extraction -----------------------------------------------------------------------------
+    def extract_triangle_mesh(self, dst=0):
+        """Halo exchange -> per-slab marching cubes with global vertex ids -> gather on rank `dst`."""
+        import torch
+        from . import geometry
+        v = self.local
+        dev = v._ctx.tdev
+        self.exchange_halos()
+        nv, nt = v._mesh_count()
+        counts = all_gather_counts([nv, nt], dev, self.group)            # [world, 2]
+        vbase = exclusive_bases(counts[:, 0])
+        V, Cc = v._mesh_vertices(nv, vertex_base=int(vbase[self.rank]))  # fills the slab's vertex-id table
+        if self.world > 1:
+            self._exchange_seam()
+        T = v._mesh_triangles(nt)
+        Vg = gather_rows(V, counts[:, 0], dst, self.group)
+        Cg = gather_rows(Cc, counts[:, 0], dst, self.group) if Cc is not None else None
+        Tg = gather_rows(T, counts[:, 1], dst, self.group)
+        if self.rank != dst:
+            return None
+        m = geometry.TriangleMesh()
+        m.vertices = Vg.cpu().numpy()
+        m.triangles = Tg.cpu().numpy()
+        if Cg is not None:
+            m.vertex_colors = Cg.cpu().numpy()
+        return m
+
+    def _exchange_seam(self):
+        """Triangles of the slab's top cube layer reference vertices owned by the first plane of the slab above:
+        that plane of the vertex-id table (R*R*4 bytes) travels one rank down."""
+        import ctypes as C
+        import torch
+        dist = _dist()
+        v = self.local
+        send, recv, nbytes = C.c_void_p(), C.c_void_p(), C.c_int64(0)
+        _lib.check(_lib.load().b2r_mesh_seam_buffers(v._ctx.handle, C.byref(v._desc), C.byref(send), C.byref(recv),
+                                                     C.byref(nbytes)))
+        n = nbytes.value // 4
+        g = (lambda r: r) if self.group is None else (lambda r: dist.get_global_rank(self.group, r))
+        ops = []
+        torch.cuda.current_stream(v._ctx.tdev).synchronize()   # the id table was written on this stream
+        if self.rank > 0:
+            ts = torch.as_tensor(_RawCuda(send.value, n), device=v._ctx.tdev)
+            ops.append(dist.P2POp(dist.isend, ts, g(self.rank - 1), self.group))
+        if self.rank < self.world - 1:
+            tr = torch.as_tensor(_RawCuda(recv.value, n), device=v._ctx.tdev)
+            ops.append(dist.P2POp(dist.irecv, tr, g(self.rank + 1), self.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+
+    def extract_point_cloud(self, dst=0):
+        from . import geometry
+        v = self.local
+        self.exchange_halos()
+        P, N, Cc = v.extract_point_cloud_device()
+        counts = all_gather_counts([int(P.shape[0])], v._ctx.tdev, self.group)[:, 0]
+        Pg = gather_rows(P, counts, dst, self.group)
+        Ng = gather_rows(N, counts, dst, self.group)
+        Cg = gather_rows(Cc, counts, dst, self.group) if Cc is not None else None
+        if self.rank != dst:
+            return None
+        pcd = geometry.PointCloud()
+        pcd._p.set_dev(Pg)
+        pcd._n.set_dev(Ng)
+        if Cg is not None:
+            pcd._c.set_dev(Cg)
+        return pcd
+
+
+# --------------------------------------------------------------------------------------------------
+# batched ICP: pairs round-robin over the ranks, no collective on the data path
+# --------------------------------------------------------------------------------------------------
+def round_robin(n_items, rank, world):
+    """Indices of the items rank `rank` owns: p with p % world == rank."""
+    return list(range(rank, n_items, world))
+
+
+def icp_round_robin(sources, targets, max_correspondence_distance, inits=None, estimation_method=None, criteria=None,
+                    gather=True, group=None):
+    """BASELINE config 4: pair p is registered on rank p % world (`registration_icp_batch` on that rank's GPU).
+    Returns the full list of RegistrationResult in pair order on every rank when `gather` (one
+    all_gather_object of the 4x4 + two scalars per pair -- results only, no point data), else {pair: result}
+    for this rank's pairs."""
+    from .pipelines import registration
+    dist = _dist()
+    rank, world = world_info(group)
+    mine = round_robin(len(sources), rank, world)
+    res = registration.registration_icp_batch([sources[p] for p in mine], [targets[p] for p in mine],
+                                              max_correspondence_distance,
+                                              None if inits is None else [inits[p] for p in mine],
+                                              estimation_method, criteria, with_correspondences=not gather)
+    local = dict(zip(mine, res))
+    if not gather:
+        return local
+    if world == 1:
+        return [local[p] for p in range(len(sources))]
+    slim = {p: (r.transformation, r.fitness, r.inlier_rmse, getattr(r, "iterations", 0), getattr(r, "converged", False))
+            for p, r in local.items()}
+    parts = [None] * world
+    dist.all_gather_object(parts, slim, group=group)
+    out = [None] * len(sources)
+    for part in parts:
+        for p, (T, f, e, it, cv) in part.items():
+            r = registration.RegistrationResult()
+            r.transformation, r.fitness, r.inlier_rmse, r.iterations, r.converged = np.asarray(T), f, e, it, cv
+            out[p] = r
+    return out

@@ -1,0 +1,110 @@
+"""Host logic of the multi-GPU layer (b200recon/parallel.py) on the gloo backend, world_size 2 and 3, CPU
+tensors: slab partition, halo exchange, variable-length gather, vertex bases, ICP pair assignment.  The same
+functions run over NCCL on the GPUs (tests/test_multi_gpu.py)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from b200recon import _lib, parallel
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, R, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        lo, hi = _lib.PAD_LO, _lib.PAD_HI
+        g = torch.Generator().manual_seed(7)
+        full = torch.rand((R, 5, 5, 2), generator=g)                 # "global volume", plane-major
+        fullc = torch.randint(0, 1 << 30, (R, 5, 5), generator=g, dtype=torch.int32)
+        zb, ze = parallel.slab_range(R, rank, world)
+        n = ze - zb
+        slab = torch.zeros((lo + n + hi, 5, 5, 2))
+        slabc = torch.zeros((lo + n + hi, 5, 5), dtype=torch.int32)
+        slab[lo:lo + n] = full[zb:ze]
+        slabc[lo:lo + n] = fullc[zb:ze]
+        parallel.exchange_halos([slab, slabc, None], n)
+        ok = True
+        for p in range(lo + n + hi):
+            z = zb - lo + p
+            want = full[z] if 0 <= z < R else torch.zeros_like(full[0])
+            wantc = fullc[z] if 0 <= z < R else torch.zeros_like(fullc[0])
+            ok &= bool(torch.equal(slab[p], want)) and bool(torch.equal(slabc[p], wantc))
+        # variable-length gather + bases
+        rows = torch.full((rank * 3 + 1, 3), float(rank), dtype=torch.float64)
+        counts = parallel.all_gather_counts([rows.shape[0], 2 * rank], torch.device("cpu"))
+        ok &= counts.shape == (world, 2) and all(int(counts[r, 0]) == r * 3 + 1 for r in range(world))
+        bases = parallel.exclusive_bases(counts[:, 0])
+        ok &= int(bases[0]) == 0 and all(int(bases[r]) == sum(3 * i + 1 for i in range(r)) for r in range(world))
+        got = parallel.gather_rows(rows, counts[:, 0], dst=0)
+        if rank == 0:
+            want = torch.cat([torch.full((r * 3 + 1, 3), float(r), dtype=torch.float64) for r in range(world)])
+            ok &= bool(torch.equal(got, want))
+        else:
+            ok &= got is None
+        # empty contribution
+        e = torch.zeros((0 if rank == 1 else 2, 3), dtype=torch.int32)
+        ce = parallel.all_gather_counts([e.shape[0]], torch.device("cpu"))[:, 0]
+        ge = parallel.gather_rows(e, ce, dst=0)
+        if rank == 0:
+            ok &= ge.shape[0] == int(ce.sum())
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,R", [(2, 8), (3, 11)])
+def test_halo_and_gather_gloo(world, R):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, R, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert sorted(res) == [(r, True) for r in range(world)]
+
+
+def test_slab_partition_and_round_robin():
+    for R, W in [(1024, 8), (512, 3), (10, 4), (2048, 8)]:
+        rs = parallel.slab_ranges(R, W)
+        assert rs[0][0] == 0 and rs[-1][1] == R
+        assert all(rs[i][1] == rs[i + 1][0] for i in range(W - 1))
+        sizes = [b - a for a, b in rs]
+        assert max(sizes) - min(sizes) <= 1
+    owned = [parallel.round_robin(64, r, 8) for r in range(8)]
+    assert sorted(sum(owned, [])) == list(range(64)) and all(len(o) == 8 for o in owned)
+    assert owned[3][:3] == [3, 11, 19]
+
+
+def test_halo_plan_messages_pair_up():
+    """Every send has the matching recv on the peer with the same plane count."""
+    W, n = 4, 6
+    plans = [parallel.halo_plan(r, W, n) for r in range(W)]
+    for r in range(W):
+        for kind, peer, first, cnt in plans[r]:
+            other = "recv" if kind == "send" else "send"
+            assert any(k == other and p == r and c == cnt for k, p, _, c in plans[peer])
+    with pytest.raises(RuntimeError):
+        parallel.halo_plan(1, 2, 1)
+
+
+def test_world_info_without_process_group():
+    assert parallel.world_info() == (0, 1)
+    assert np.array_equal(parallel.exclusive_bases([3, 0, 5]), [0, 3, 3])
