@@ -47,7 +47,7 @@ int b2r_ctx_create(int device, b2r_ctx** out) {
 int b2r_ctx_destroy(b2r_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
-    b2r::Scratch* all[] = {&c->frame_dm, &c->frame_mip, &c->frame_rgba, &c->frame_raw_depth, &c->frame_raw_color, &c->frame_f32,
+    b2r::Scratch* all[] = {&c->frame_dm, &c->frame_mip, &c->frame_rgba, &c->frame_raw_depth, &c->frame_raw_color, &c->frame_f32, &c->integ_hdr, &c->integ_rec,
                            &c->small, &c->scan_a, &c->scan_b, &c->mc_code, &c->mc_flags, &c->mc_block_counts,
                            &c->mc_vert_id, &c->pc_block_counts, &c->icp_a, &c->icp_b, &c->icp_c, &c->icp_d,
                            &c->icp_e, &c->icp_f};

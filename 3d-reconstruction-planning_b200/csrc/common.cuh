@@ -62,6 +62,7 @@ struct b2r_ctx {
     int64_t launches = 0;
     // frame staging (prepared frame: {depth_m, multiplier} float2 + packed RGBA)
     b2r::Scratch frame_dm, frame_mip, frame_rgba, frame_raw_depth, frame_raw_color, frame_f32;
+    b2r::Scratch integ_hdr, integ_rec;   // integrate work items (tsdf_integrate.cu)
     b2r::Scratch small;       // counters, per-frame scalars (zero-initialised on creation)
     b2r::Scratch scan_a, scan_b;
     // marching cubes

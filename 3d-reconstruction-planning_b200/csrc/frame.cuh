@@ -6,6 +6,8 @@ namespace b2r {
 // slots inside ctx->small (uint32 index for 32-bit values, uint64 index for 64-bit values; the two
 // index spaces are kept apart: 32-bit slots live in bytes [0,1024), 64-bit slots in [1024,4096)).
 constexpr int SMALL_DMAX = 0;          // uint32: bits of the frame's max depth
+constexpr int SMALL_ITEMS = 8;         // uint32: integrate work items planned for the frame
+constexpr int SMALL_NEXT = 9;          // uint32: next work item to hand out
 constexpr int SMALL_TOTAL64 = 128;     // uint64 index (byte 1024): scan totals
 constexpr int SMALL_TOTAL64_B = 129;
 constexpr int SMALL_TOTAL64_C = 130;
