@@ -30,7 +30,8 @@ __global__ void depth_to_float_kernel(const void* __restrict__ depth, int dtype,
 // fetches everything a voxel needs from the frame with a single 16-byte gather.
 __global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, int convert, float scale, float trunc,
                                      const void* __restrict__ color, int color_mode, int H, int W, float cx, float cy,
-                                     float ffl_inv_x, float ffl_inv_y, float4* __restrict__ px,
+                                     float ffl_inv_x, float ffl_inv_y, float2* __restrict__ px,
+                                     uint32_t* __restrict__ pcol,
                                      const MipDesc M, unsigned int* __restrict__ mip,
                                      unsigned int* __restrict__ dmax_bits) {
     const int u = blockIdx.x * blockDim.x + threadIdx.x;
@@ -55,7 +56,8 @@ __global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, 
         } else if (color_mode == 2) {
             c = __float_as_uint(((const float*)color)[i]);
         }
-        px[i] = make_float4(d, m, __uint_as_float(c), 0.0f);
+        px[i] = make_float2(d, m);
+        pcol[i] = c;
     }
     // Max-depth pyramid (cells of 8, 16, 32, 64, 128 pixels; positive floats order like their bit patterns)
     // and the frame-wide maximum.  The integrate kernel bounds the depth any voxel of a lane's z chunk can
@@ -96,7 +98,8 @@ int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, dou
                   const void* d_color, int color_mode, const b2r_intrinsic* K, cudaStream_t stream) {
     const int H = K->height, W = K->width;
     const size_t n = (size_t)H * W;
-    if (ctx->frame_dm.ensure(n * sizeof(float4))) return -102;
+    if (ctx->frame_dm.ensure(n * sizeof(float2))) return -102;
+    if (ctx->frame_rgba.ensure(n * sizeof(uint32_t))) return -102;
     const MipDesc M = mip_desc(H, W);
     if (ctx->frame_mip.ensure((size_t)(M.total + 1) * sizeof(float))) return -102;
     B2R_CUDA(cudaMemsetAsync(ctx->frame_mip.ptr, 0, (size_t)(M.total + 1) * sizeof(float), stream));
@@ -106,7 +109,8 @@ int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, dou
     dim3 block(128), grid(cdiv(W, 128), H);
     frame_prepare_kernel<<<grid, block, 0, stream>>>(d_depth, dtype, convert, (float)depth_scale, (float)depth_trunc,
                                                      d_color, color_mode, H, W, (float)K->cx, (float)K->cy, ffl_inv_x,
-                                                     ffl_inv_y, (float4*)ctx->frame_dm.ptr, M, mip, dmax);
+                                                     ffl_inv_y, (float2*)ctx->frame_dm.ptr, (uint32_t*)ctx->frame_rgba.ptr, M,
+                                                     mip, dmax);
     B2R_LAUNCH_CHECK(ctx);
     return 0;
 }
