@@ -191,6 +191,7 @@ class SlabVolume:
     def exchange_halos(self):
         """One-plane-below / two-planes-above halo of {tsdf, weight} and colour from the neighbour slabs."""
         if not self._halo_valid:
+            self.local._ctx.join()   # the planes are sent straight from the volume's tensors
             exchange_halos([self.local._tsdfw, self.local._color], self.z_end - self.z_begin, self.rank, self.world,
                            self.group)
             self._halo_valid = True

@@ -106,11 +106,19 @@ class UniformTSDFVolume(TSDFVolume):
 
     def updates(self):
         """Number of voxel updates counted since the last reset (needs count_updates=True)."""
+        self._ctx.join()
         return int(self._updates.item())
+
+    def __del__(self):
+        # the volume's tensors go back to torch's allocator: no streaming kernel may still be writing them
+        try:
+            self._ctx.join()
+        except Exception:
+            pass
 
     def reset(self):
         c = self._ctx
-        _lib.check(_lib.load().b2r_volume_reset(c.handle, C.byref(self._desc), c.stream()))
+        _lib.check(_lib.load().b2r_volume_reset(c.handle, C.byref(self._desc), c.stream()))   # joins the side stream
         self._updates.zero_()
 
     # ------------------------------------------------------------------ raw access (tests, persistence)

@@ -52,6 +52,17 @@ class Context:
         _lib.check(_lib.load().b2r_ctx_kernel_time(self.handle, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def join(self):
+        """Order the current torch stream after every integration queued so far (their streaming kernels run on
+        a stream owned by the library context).  Needed only before touching a volume's tensors directly."""
+        _lib.check(_lib.load().b2r_ctx_join(self.handle, self.stream()))
+
+    def updates_mirror(self):
+        """Pinned-host copy of the update counter of the newest completed integrate call (see b200recon.h)."""
+        n = C.c_uint64(0)
+        _lib.check(_lib.load().b2r_ctx_updates_mirror(self.handle, C.byref(n)))
+        return n.value
+
     def sync(self):
         _lib.check(_lib.load().b2r_ctx_sync(self.handle, self.stream()))
 

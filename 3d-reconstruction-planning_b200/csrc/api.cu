@@ -1,5 +1,6 @@
 // Context management + error reporting for the C ABI (include/b200recon.h).
 #include <cstdarg>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -38,6 +39,15 @@ int b2r_ctx_create(int device, b2r_ctx** out) {
     c->sm_count = prop.multiProcessorCount;
     if (c->small.ensure(4096)) { delete c; return -102; }
     B2R_CUDA(cudaMemset(c->small.ptr, 0, c->small.bytes));
+    {
+        const char* e2 = getenv("B2R_ASYNC");
+        c->async_items = !(e2 && e2[0] == '0');
+    }
+    B2R_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    for (auto& f : c->fslot) {
+        B2R_CUDA(cudaEventCreateWithFlags(&f.ev_plan, cudaEventDisableTiming));
+        B2R_CUDA(cudaEventCreateWithFlags(&f.ev_items, cudaEventDisableTiming));
+    }
     c->pinned_bytes = 1 << 16;
     B2R_CUDA(cudaMallocHost(&c->pinned, c->pinned_bytes));
     *out = c;
@@ -47,7 +57,15 @@ int b2r_ctx_create(int device, b2r_ctx** out) {
 int b2r_ctx_destroy(b2r_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
-    b2r::Scratch* all[] = {&c->frame_dm, &c->frame_mip, &c->frame_rgba, &c->frame_raw_depth, &c->frame_raw_color, &c->frame_f32, &c->integ_hdr, &c->integ_rec,
+    if (c->side) cudaStreamSynchronize(c->side);
+    for (auto& f : c->fslot) {
+        b2r::Scratch* fs[] = {&f.dm, &f.rgba, &f.mip, &f.hdr, &f.rec, &f.counters};
+        for (auto* s : fs) s->release();
+        if (f.ev_plan) cudaEventDestroy(f.ev_plan);
+        if (f.ev_items) cudaEventDestroy(f.ev_items);
+    }
+    if (c->side) cudaStreamDestroy(c->side);
+    b2r::Scratch* all[] = {&c->frame_raw_depth, &c->frame_raw_color, &c->frame_f32,
                            &c->small, &c->scan_a, &c->scan_b, &c->mc_code, &c->mc_flags, &c->mc_block_counts,
                            &c->mc_vert_id, &c->pc_block_counts, &c->icp_a, &c->icp_b, &c->icp_c, &c->icp_d,
                            &c->icp_e, &c->icp_f};
@@ -86,9 +104,23 @@ int b2r_ctx_kernel_time(b2r_ctx* c, double* ms_total, int64_t* n_launches) {
     return 0;
 }
 
+int b2r_ctx_join(b2r_ctx* c, void* stream) {
+    B2R_CHECK(c, -1, "b2r_ctx_join: NULL ctx");
+    B2R_CUDA(cudaSetDevice(c->device));
+    B2R_CUDA(b2r::join_side(c, b2r::S(stream)));
+    return 0;
+}
+
+int b2r_ctx_updates_mirror(b2r_ctx* c, unsigned long long* out) {
+    B2R_CHECK(c && out, -1, "b2r_ctx_updates_mirror: NULL argument");
+    *out = *(volatile unsigned long long*)((char*)c->pinned + 1024);
+    return 0;
+}
+
 int b2r_ctx_sync(b2r_ctx* c, void* stream) {
     B2R_CHECK(c, -1, "b2r_ctx_sync: NULL ctx");
     B2R_CUDA(cudaSetDevice(c->device));
+    B2R_CUDA(b2r::join_side(c, b2r::S(stream)));
     B2R_CUDA(cudaStreamSynchronize(b2r::S(stream)));
     return 0;
 }

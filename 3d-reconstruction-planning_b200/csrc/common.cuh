@@ -56,13 +56,26 @@ struct Scratch {
 
 }  // namespace b2r
 
+// Everything one frame needs between its preparation and its items kernel.  Two slots alternate so that
+// frame i+1 is prepared and planned on the caller's stream while frame i still streams on the side stream.
+struct b2r_frame_slot {
+    b2r::Scratch dm, rgba, mip;      // prepared frame: {depth, multiplier} pairs, colour words, max-depth pyramid
+    b2r::Scratch hdr, rec, counters; // work items of the frame and their two counters
+    cudaEvent_t ev_plan = nullptr, ev_items = nullptr;
+    bool busy = false;               // ev_items has been recorded
+};
+
 struct b2r_ctx {
     int device = 0;
     int sm_count = 148;
     int64_t launches = 0;
     // frame staging (prepared frame: {depth_m, multiplier} float2 + packed RGBA)
-    b2r::Scratch frame_dm, frame_mip, frame_rgba, frame_raw_depth, frame_raw_color, frame_f32;
-    b2r::Scratch integ_hdr, integ_rec;   // integrate work items (tsdf_integrate.cu)
+    b2r::Scratch frame_raw_depth, frame_raw_color, frame_f32;
+    b2r_frame_slot fslot[2];
+    int cur_slot = 0;
+    cudaStream_t side = nullptr;     // items kernels run here (B2R_ASYNC=0: on the caller's stream)
+    bool async_items = true;
+    cudaEvent_t last_items = nullptr;   // completion of the newest items kernel on the side stream
     b2r::Scratch small;       // counters, per-frame scalars (zero-initialised on creation)
     b2r::Scratch scan_a, scan_b;
     // marching cubes
@@ -83,6 +96,10 @@ struct b2r_ctx {
 };
 
 namespace b2r {
+// Orders `st` after every items kernel launched so far (they run on the context's side stream).
+static inline cudaError_t join_side(b2r_ctx* ctx, cudaStream_t st) {
+    return ctx->last_items ? cudaStreamWaitEvent(st, ctx->last_items, 0) : cudaSuccess;
+}
 static inline cudaStream_t S(void* s) { return (cudaStream_t)s; }
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 }  // namespace b2r

@@ -158,6 +158,7 @@ extern "C" {
 int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_points, void* stream) {
     B2R_CHECK(ctx && vol && vol->d_tsdfw && n_points, -1, "b2r_extract_points_count: NULL argument");
     B2R_CUDA(cudaSetDevice(ctx->device));
+    B2R_CUDA(join_side(ctx, S(stream)));   // items kernels of earlier integrate calls run on the side stream
     cudaStream_t st = S(stream);
     const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
     *n_points = 0;

@@ -94,22 +94,22 @@ MipDesc mip_desc(int H, int W) {
     return M;
 }
 
-int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
+int prepare_frame(b2r_ctx* ctx, b2r_frame_slot* slot, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
                   const void* d_color, int color_mode, const b2r_intrinsic* K, cudaStream_t stream) {
     const int H = K->height, W = K->width;
     const size_t n = (size_t)H * W;
-    if (ctx->frame_dm.ensure(n * sizeof(float2))) return -102;
-    if (ctx->frame_rgba.ensure(n * sizeof(uint32_t))) return -102;
+    if (slot->dm.ensure(n * sizeof(float2))) return -102;
+    if (slot->rgba.ensure(n * sizeof(uint32_t))) return -102;
     const MipDesc M = mip_desc(H, W);
-    if (ctx->frame_mip.ensure((size_t)(M.total + 1) * sizeof(float))) return -102;
-    B2R_CUDA(cudaMemsetAsync(ctx->frame_mip.ptr, 0, (size_t)(M.total + 1) * sizeof(float), stream));
-    unsigned int* mip = (unsigned int*)ctx->frame_mip.ptr;
+    if (slot->mip.ensure((size_t)(M.total + 1) * sizeof(float))) return -102;
+    B2R_CUDA(cudaMemsetAsync(slot->mip.ptr, 0, (size_t)(M.total + 1) * sizeof(float), stream));
+    unsigned int* mip = (unsigned int*)slot->mip.ptr;
     unsigned int* dmax = mip + M.total;   // frame-wide maximum depth sits behind the pyramid
     const float ffl_inv_x = 1.0f / (float)K->fx, ffl_inv_y = 1.0f / (float)K->fy;
     dim3 block(128), grid(cdiv(W, 128), H);
     frame_prepare_kernel<<<grid, block, 0, stream>>>(d_depth, dtype, convert, (float)depth_scale, (float)depth_trunc,
                                                      d_color, color_mode, H, W, (float)K->cx, (float)K->cy, ffl_inv_x,
-                                                     ffl_inv_y, (float2*)ctx->frame_dm.ptr, (uint32_t*)ctx->frame_rgba.ptr, M,
+                                                     ffl_inv_y, (float2*)slot->dm.ptr, (uint32_t*)slot->rgba.ptr, M,
                                                      mip, dmax);
     B2R_LAUNCH_CHECK(ctx);
     return 0;

@@ -20,7 +20,7 @@ MipDesc mip_desc(int H, int W);
 
 // Fills ctx->frame_mip (max-depth pyramid) and ctx->frame_dm (float4 {depth_m, multiplier, colour bits, 0} per pixel) for one frame.
 // color_mode: 0 none, 1 uint8 x3, 2 float32 gray.
-int prepare_frame(b2r_ctx* ctx, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
+int prepare_frame(b2r_ctx* ctx, b2r_frame_slot* slot, const void* d_depth, int dtype, int convert, double depth_scale, double depth_trunc,
                   const void* d_color, int color_mode, const b2r_intrinsic* K, cudaStream_t stream);
 
 void invert4(const double* m, double* out);

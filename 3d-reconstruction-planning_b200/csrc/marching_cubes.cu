@@ -249,6 +249,7 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
                            void* stream) {
     B2R_CHECK(ctx && vol && vol->d_tsdfw && n_vertices && n_triangles, -1, "b2r_extract_mesh_count: NULL argument");
     B2R_CUDA(cudaSetDevice(ctx->device));
+    B2R_CUDA(join_side(ctx, S(stream)));   // items kernels of earlier integrate calls run on the side stream
     cudaStream_t st = S(stream);
     const int R = vol->resolution, zb = vol->z_begin, ze = vol->z_end, nz = ze - zb;
     *n_vertices = 0; *n_triangles = 0;

@@ -39,6 +39,9 @@ WORKLOADS = {
     "tsdf512": (512, 1.024, 0.01, 64, 0.5),
     "tsdf1024": (1024, 2.048, 0.01, 256, 0.9),
 }
+# dram__bytes_read.sum + dram__bytes_write.sum of one integrate_items launch from the committed ncu --set full
+# capture of this command (profiles/r01_integrate_v9_ncu.txt); per launch, like roofline.achieved
+NCU_TRAFFIC = {"tsdf1024": 869561856 + 700835840}
 B_UPD = 24  # algorithmic bytes per voxel update: float2 R+W (16) + packed colour R+W (8)  
 
 
@@ -184,7 +187,7 @@ def run_gpu(args):
     zb, ze = R * rank // world, R * (rank + 1) // world
     vol = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
                                                       syn.volume_origin(L), z_range=(zb, ze), device=local)
-    vol.count_updates = True
+    vol.count_updates = False   # switched on for the counting pass and the e2e pass only
 
     # synthetic frames: ray-cast on this GPU (resident in HBM), raw uint16 depth + uint8 colour
     nf = min(len(poses), max(args.steps + args.warmup, 1))
@@ -204,7 +207,6 @@ def run_gpu(args):
     # pinned host copies for the e2e arm
     d16_h = d16.cpu().pin_memory()
     rgb_h = rgb.cpu().pin_memory()
-    res_h = torch.zeros(1, dtype=torch.int64).pin_memory()
     torch.cuda.synchronize()
 
     def barrier():
@@ -217,9 +219,10 @@ def run_gpu(args):
         vol.integrate_device(depth_f[k], rgb[k], intr, exts[k])
 
     def step_e2e(i):
+        # pinned HOST frame -> H2D + conversion + plan + streaming kernel; the step's result (running update
+        # count, 8 bytes) is copied device -> pinned host by the library right behind the kernel
         k = i % nf
         vol.integrate_host(d16_h[k], rgb_h[k], intr, exts[k])
-        res_h.copy_(vol._updates, non_blocking=True)   # the step's result (running update count), 8 B D2H
 
     def timed(step, steps, warmup, sample_clocks=False):
         vol.reset()
@@ -235,6 +238,7 @@ def run_gpu(args):
         e0.record()
         for i in range(warmup, warmup + steps):
             step(i)
+        ctx.join()          # the streaming kernels run on the library's side stream: e1 goes behind the last one
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
@@ -250,16 +254,24 @@ def run_gpu(args):
             upd = int(u.item())
         return ms, upd, launches, clocks
 
-    ms, upd, launches, clocks = timed(step_dev, args.steps, args.warmup, sample_clocks=True)
-    # dominant kernel alone: CUDA events around every tsdf_integrate launch (same steps again)
+    ms, _, launches, clocks = timed(step_dev, args.steps, args.warmup, sample_clocks=True)
+    # dominant kernel alone: CUDA events (on the stream it is launched on) around every integrate_items launch
+    # of the same steps, run again
     ctx.kernel_timing(True)
-    _ms2, upd_k, _, _ = timed(step_dev, args.steps, args.warmup)
+    timed(step_dev, args.steps, args.warmup)
     ctx.kernel_timing(False)
     k_ms, k_n = ctx.kernel_time()
     k_n_timed = args.steps
     # kernel_time covers warm-up launches too; time only the last `steps` launches' share
     k_ms_timed = k_ms * k_n_timed / max(k_n, 1)
+    # voxel updates of exactly these steps: the same sequence replayed with the counting kernel variant (the
+    # count is a deterministic function of the frame sequence since reset)
+    vol.count_updates = True
+    _, upd, _, _ = timed(step_dev, args.steps, args.warmup)
+    upd_k = upd
     e_ms, e_upd, _, _ = timed(step_e2e, args.steps, args.warmup)
+    mirror = ctx.updates_mirror()
+    assert mirror == vol.updates(), "host mirror of the step result disagrees with the device counter"
 
     out = None
     if rank == 0:
@@ -284,9 +296,11 @@ def run_gpu(args):
             "clocks": clocks,
             "e2e": {"value": args.steps / (e_ms * 1e-3), "unit": "frames/s",
                     "h2d_bytes_per_step": int(d16_h[0].numel() * 2 + rgb_h[0].numel()), "d2h_bytes_per_step": 8,
+                    "note": "host frames in pinned memory; H2D copies, conversion and planning of frame i+1 overlap "
+                            "the streaming kernel of frame i (library side stream)",
                     "voxel_updates_per_s": e_upd / (e_ms * 1e-3)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "tsdf_integrate_kernel", "peak_source": peak_src,
+                         "traffic": NCU_TRAFFIC.get(args.workload), "kernel": "integrate_items_kernel", "peak_source": peak_src,
                          "kernel_ms_per_launch": k_ms_timed / max(args.steps, 1),
                          "alg_bytes_per_launch": alg_bytes, "bytes_per_update": B_UPD,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
@@ -300,7 +314,7 @@ def run_gpu(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=256)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="tsdf1024", choices=sorted(WORKLOADS))

@@ -64,7 +64,18 @@ int b2r_ctx_create(int device, b2r_ctx** out);
 int b2r_ctx_destroy(b2r_ctx* ctx);
 /* Number of kernels this context has launched so far (bench.py "gpu_launches"). */
 int b2r_ctx_launch_count(b2r_ctx* ctx, int64_t* out);
-int b2r_ctx_sync(b2r_ctx* ctx, void* stream); /* blocking */
+/* b2r_integrate* return after queueing the frame's preparation and planning on `stream`; the streaming kernel
+ * itself runs on a stream owned by the context so that the NEXT frame can be prepared meanwhile.  Every entry
+ * point of this library that reads or writes a volume orders itself after that work; code that touches the
+ * volume's buffers directly (e.g. an NCCL send of a halo plane) calls b2r_ctx_join first: it makes `stream` wait
+ * (on the device, the host does not block) for every integration queued so far.  B2R_ASYNC=0 in the
+ * environment keeps everything on the caller's stream. */
+int b2r_ctx_join(b2r_ctx* ctx, void* stream);
+int b2r_ctx_sync(b2r_ctx* ctx, void* stream); /* join + blocking */
+/* Host mirror of the update counter passed to the most recent b2r_integrate* call as d_updates: the library
+ * copies it (8 bytes, device -> pinned host) right behind each frame's streaming kernel.  Not blocking: valid
+ * for a frame once that frame has completed (b2r_ctx_sync). */
+int b2r_ctx_updates_mirror(b2r_ctx* ctx, unsigned long long* out);
 /* Per-kernel timing of the dominant kernel (tsdf_integrate) with CUDA events recorded on the launching
  * stream around each launch: enable=1 starts (and clears) collection, enable=0 stops it.
  * b2r_ctx_kernel_time is blocking: total milliseconds and number of launches collected. */
