@@ -40,8 +40,8 @@ WORKLOADS = {
     "tsdf1024": (1024, 2.048, 0.01, 256, 0.9),
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of one integrate_items launch from the committed ncu --set full
-# capture of this command (profiles/r01_integrate_v9_ncu.txt); per launch, like roofline.achieved
-NCU_TRAFFIC = {"tsdf1024": 869561856 + 700835840}
+# capture of this command (profiles/r01_integrate_v10_ncu.txt); per launch, like roofline.achieved
+NCU_TRAFFIC = {"tsdf1024": 881662208 + 702442752}
 B_UPD = 24  # algorithmic bytes per voxel update: float2 R+W (16) + packed colour R+W (8)  
 
 
