@@ -6,7 +6,7 @@ Every operation runs as a hand-written sm_100a CUDA kernel of libb200recon.so, r
 C ABI in include/b200recon.h.  There is no CPU fallback: without the built library or without a B200
 the first device call raises.
 """
-from . import camera, geometry, io, pipelines, utility, visualization  # noqa: F401
+from . import camera, geometry, cloud_ops, io, pipelines, utility, visualization  # noqa: F401
 from ._lib import B2RError  # noqa: F401
 
 __version__ = "0.1.0"

@@ -44,6 +44,8 @@ class Scene(C.Structure):
                 ("n_tris", C.c_int32), ("mesh_min", C.c_float * 3), ("mesh_max", C.c_float * 3)]
 
 
+SEARCH_KNN = 0
+SEARCH_HYBRID = 2
 PAD_LO = 1
 PAD_HI = 2
 
@@ -76,6 +78,11 @@ SIGNATURES = {
     "b2r_extract_points_emit": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, c_vp, c_vp]),
     "b2r_icp_batch": (C.c_int, [c_vp, C.c_int, c_vp, c_i64p, c_vp, c_vp, c_i64p, c_vp, c_vp, c_vp, c_dp,
                                 C.POINTER(IcpParams), C.POINTER(IcpResult), c_vp, c_vp]),
+    "b2r_voxel_down_sample": (C.c_int, [c_vp, c_vp, c_vp, c_vp, C.c_int64, C.c_double, c_vp, c_vp, c_vp, c_i64p, c_vp]),
+    "b2r_estimate_normals": (C.c_int, [c_vp, c_vp, C.c_int64, C.c_int, C.c_double, C.c_int, c_vp, c_vp, c_vp]),
+    "b2r_statistical_outlier": (C.c_int, [c_vp, c_vp, C.c_int64, C.c_int, C.c_double, c_vp, c_i64p, c_vp]),
+    "b2r_color_gradient": (C.c_int, [c_vp, c_vp, c_vp, c_vp, C.c_int64, C.c_double, C.c_int, c_vp, c_vp]),
+    "b2r_knn_search": (C.c_int, [c_vp, c_vp, C.c_int64, c_vp, C.c_int64, C.c_int, C.c_double, C.c_int, c_vp, c_vp, c_vp]),
     "b2r_raycast_scene": (C.c_int, [c_vp, C.POINTER(Scene), c_vp, c_vp, c_vp, c_vp]),
 }
 

@@ -96,8 +96,6 @@ def _check_icp_args(target, max_correspondence_distance, estimation_method):
     if kind in (1, 2) and not target.has_normals():
         raise RuntimeError("TransformationEstimationPointToPlane and TransformationEstimationColoredICP require "
                            "pre-computed normal vectors for target PointCloud.")
-    if kind == 2:
-        raise NotImplementedError("registration_colored_icp (SURVEY.md 8(f) row f3) is not built yet")
     return kind
 
 
@@ -133,16 +131,28 @@ def registration_icp_batch(sources, targets, max_correspondence_distance, inits=
 
     S = cat([s._p.get_dev() for s in sources]).contiguous()
     T = cat([g._p.get_dev() for g in targets]).contiguous()
-    N = cat([g._n.get_dev() for g in targets]).contiguous() if kind == 1 else None
+    N = cat([g._n.get_dev() for g in targets]).contiguous() if kind >= 1 else None
+    SC = TC = TG = None
+    if kind == 2:
+        # Open3D RegistrationColoredICP: both clouds need colours; the target's colour gradient is precomputed with
+        # KDTreeSearchParamHybrid(radius = 2 * max_correspondence_distance, max_nn = 30)
+        from .. import cloud_ops
+        for s_, g_ in zip(sources, targets):
+            if not (s_.has_colors() and g_.has_colors()):
+                raise RuntimeError("ColoredICP requires source and target PointClouds with colors.")
+        SC = cat([s_._c.get_dev() for s_ in sources]).contiguous()
+        TC = cat([g_._c.get_dev() for g_ in targets]).contiguous()
+        TG = cat([cloud_ops.color_gradient(g_, 2.0 * float(max_correspondence_distance), 30) for g_ in targets]).contiguous()
     init = np.ascontiguousarray(np.stack([np.eye(4) if inits is None or inits[p] is None else
                                           np.asarray(inits[p], np.float64).reshape(4, 4) for p in range(n)]))
     prm = _lib.IcpParams(float(max_correspondence_distance), criteria.relative_fitness, criteria.relative_rmse,
-                         criteria.max_iteration, kind, 0.968)
+                         criteria.max_iteration, kind, float(getattr(estimation_method, "lambda_geometric", 0.968)))
     res = (_lib.IcpResult * n)()
     corr = t.empty((int(src_off[n]),), dtype=t.int32, device=c.tdev) if with_correspondences else None
     _lib.check(_lib.load().b2r_icp_batch(c.handle, n, runtime.ptr(S), src_off.ctypes.data_as(_lib.c_i64p),
                                          runtime.ptr(T), runtime.ptr(N), tgt_off.ctypes.data_as(_lib.c_i64p),
-                                         None, None, None, init.ctypes.data_as(_lib.c_dp), C.byref(prm), res,
+                                         runtime.ptr(SC), runtime.ptr(TC), runtime.ptr(TG),
+                                         init.ctypes.data_as(_lib.c_dp), C.byref(prm), res,
                                          runtime.ptr(corr), c.stream()))
     corr_h = corr.cpu().numpy() if corr is not None else None
     out = []
@@ -176,5 +186,10 @@ def evaluate_registration(source, target, max_correspondence_distance, transform
 
 def registration_colored_icp(source, target, max_correspondence_distance, init=None, estimation_method=None,
                              criteria=None):
-    """stitcher.py:94-102 -- SURVEY.md 8(f) row f3 ("next"); not built yet, fails loudly."""
-    raise NotImplementedError("registration_colored_icp (SURVEY.md 8(f) row f3) is not built yet")
+    """Open3D pipelines.registration.registration_colored_icp (stitcher.py:94-102): colour gradient of
+    the target (b2r_color_gradient) + ICP with a geometric and a photometric residual per correspondence."""
+    estimation_method = estimation_method or TransformationEstimationForColoredICP()
+    if estimation_method._kind != 2:
+        raise RuntimeError("registration_colored_icp needs TransformationEstimationForColoredICP")
+    return registration_icp_batch([source], [target], max_correspondence_distance, [init], estimation_method,
+                                  criteria)[0]

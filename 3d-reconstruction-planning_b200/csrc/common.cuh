@@ -87,6 +87,8 @@ struct b2r_ctx {
     int64_t pc_n = 0;
     // ICP
     b2r::Scratch icp_a, icp_b, icp_c, icp_d, icp_e, icp_f;
+    // point-cloud preprocessing (cloud.cu): grid hash, sorted points, per-cell accumulators
+    b2r::Scratch cl_a, cl_b, cl_c, cl_d;
     // optional CUDA-event timing of the dominant kernel
     bool timing = false;
     std::vector<cudaEvent_t> ev_pool;

@@ -353,8 +353,28 @@ struct IcpArgs {
     double rel_fitness, rel_rmse;
     int max_iter;
     int estimation;
+    // colored ICP (estimation 2): source colours (original order), target intensity / colour gradient sorted by cell
+    const double* src_col;
+    const double* s_it;
+    const double* s_grad;
+    double sqrt_lg, sqrt_lp;   // sqrt(lambda_geometric), sqrt(1 - lambda_geometric)
 };
 
+// target intensity (r+g+b)/3 and colour gradient in cell-sorted order (s_idx maps sorted position -> point of the pair)
+__global__ void __launch_bounds__(256) icp_gather_color_kernel(const double* __restrict__ tgt_col, const double* __restrict__ tgt_grad,
+                                                               const IcpPair* __restrict__ pairs, const int32_t* __restrict__ s_idx,
+                                                               double* __restrict__ s_it, double* __restrict__ s_grad) {
+    const IcpPair P = pairs[blockIdx.y];
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n_tgt) return;
+    const long long pos = P.tgt_off + i;                       // sorted positions of a pair occupy its own range
+    const long long g = P.tgt_off + (long long)s_idx[pos];
+    s_it[pos] = (tgt_col[g * 3] + tgt_col[g * 3 + 1] + tgt_col[g * 3 + 2]) / 3.0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) s_grad[pos * 3 + k] = tgt_grad[g * 3 + k];
+}
+
+template <int EST>
 __global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_constant__ IcpArgs A) {
     const int p = blockIdx.y;
     IcpState& St = A.states[p];
@@ -445,7 +465,41 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_c
         const double tx = A.s_pts[bestpos * 3], ty = A.s_pts[bestpos * 3 + 1], tz = A.s_pts[bestpos * 3 + 2];
         acc[0] += 1.0;
         acc[1] += best;
-        if (A.estimation == 1) {
+        if (EST == 2) {
+            // TransformationEstimationForColoredICP: geometric + photometric residual per correspondence
+            const double nt[3] = {A.s_nrm[bestpos * 3], A.s_nrm[bestpos * 3 + 1], A.s_nrm[bestpos * 3 + 2]};
+            const double dit[3] = {A.s_grad[bestpos * 3], A.s_grad[bestpos * 3 + 1], A.s_grad[bestpos * 3 + 2]};
+            const double dn = (q[0] - tx) * nt[0] + (q[1] - ty) * nt[1] + (q[2] - tz) * nt[2];
+            const double* sc = A.src_col + (P.src_off + i) * 3;
+            const double is = (sc[0] + sc[1] + sc[2]) / 3.0;
+            const double vp[3] = {q[0] - dn * nt[0], q[1] - dn * nt[1], q[2] - dn * nt[2]};
+            const double is0 = (dit[0] * (vp[0] - tx) + dit[1] * (vp[1] - ty) + dit[2] * (vp[2] - tz)) + A.s_it[bestpos];
+            const double M[9] = {1.0 - nt[0] * nt[0], -nt[0] * nt[1], -nt[0] * nt[2], -nt[0] * nt[1], 1.0 - nt[1] * nt[1],
+                                 -nt[1] * nt[2], -nt[0] * nt[2], -nt[1] * nt[2], 1.0 - nt[2] * nt[2]};
+            double dm[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) dm[c] = (-dit[0]) * M[c] + (-dit[1]) * M[3 + c] + (-dit[2]) * M[6 + c];
+            double J[2][6], r[2];
+            const double cg[3] = {q[1] * nt[2] - q[2] * nt[1], q[2] * nt[0] - q[0] * nt[2], q[0] * nt[1] - q[1] * nt[0]};
+            const double cm[3] = {q[1] * dm[2] - q[2] * dm[1], q[2] * dm[0] - q[0] * dm[2], q[0] * dm[1] - q[1] * dm[0]};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                J[0][k] = A.sqrt_lg * cg[k]; J[0][3 + k] = A.sqrt_lg * nt[k];
+                J[1][k] = A.sqrt_lp * cm[k]; J[1][3 + k] = A.sqrt_lp * dm[k];
+            }
+            r[0] = A.sqrt_lg * dn;
+            r[1] = A.sqrt_lp * (is - is0);
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                int k = 2;
+#pragma unroll
+                for (int a = 0; a < 6; ++a)
+#pragma unroll
+                    for (int b = a; b < 6; ++b) acc[k++] += J[e][a] * J[e][b];
+#pragma unroll
+                for (int a = 0; a < 6; ++a) acc[23 + a] += J[e][a] * r[e];
+            }
+        } else if (EST == 1) {
             const double nx = A.s_nrm[bestpos * 3], ny = A.s_nrm[bestpos * 3 + 1], nz = A.s_nrm[bestpos * 3 + 2];
             const double r = (q[0] - tx) * nx + (q[1] - ty) * ny + (q[2] - tz) * nz;
             const double J[6] = {q[1] * nz - q[2] * ny, q[2] * nx - q[0] * nz, q[0] * ny - q[1] * nx, nx, ny, nz};
@@ -519,7 +573,7 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_c
     double upd[16];
     for (int i = 0; i < 16; ++i) upd[i] = (i % 5 == 0) ? 1.0 : 0.0;
     if (K > 0) {
-        if (A.estimation == 1) {
+        if (EST >= 1) {
             double JTJ[36], nb[6], x[6];
             int k = 2;
             for (int a = 0; a < 6; ++a)
@@ -566,12 +620,17 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
     B2R_CHECK(n_pairs >= 0, -5, "b2r_icp_batch: negative pair count");
     // Open3D RegistrationICP: LogError("Invalid max_correspondence_distance.")
     B2R_CHECK(params->max_correspondence_distance > 0.0, -10, "Invalid max_correspondence_distance.");
-    B2R_CHECK(params->estimation == 0 || params->estimation == 1, -11,
-              "b2r_icp_batch: estimation %d is not implemented (0 point-to-point, 1 point-to-plane)", params->estimation);
+    B2R_CHECK(params->estimation >= 0 && params->estimation <= 2, -11,
+              "b2r_icp_batch: unknown estimation %d (0 point-to-point, 1 point-to-plane, 2 colored)", params->estimation);
     // Open3D: "TransformationEstimationPointToPlane ... require pre-computed normal vectors for target PointCloud."
-    B2R_CHECK(params->estimation != 1 || d_tgt_normals, -12,
+    B2R_CHECK(params->estimation == 0 || d_tgt_normals, -12,
               "TransformationEstimationPointToPlane and TransformationEstimationColoredICP require pre-computed "
               "normal vectors for target PointCloud.");
+    // Open3D RegistrationColoredICP: LogError when either cloud has no colours; the gradient comes from b2r_color_gradient
+    B2R_CHECK(params->estimation != 2 || (d_src_colors && d_tgt_colors && d_tgt_color_grad), -13,
+              "ColoredICP requires source and target PointClouds with colors (and the target's colour gradient).");
+    B2R_CHECK(params->estimation != 2 || (params->lambda_geometric >= 0.0 && params->lambda_geometric <= 1.0), -13,
+              "ColoredICP: lambda_geometric must be in [0, 1]");
     if (n_pairs == 0) return 0;
     B2R_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t st = S(stream);
@@ -656,15 +715,31 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
         B2R_LAUNCH_CHECK(ctx);
     }
 
+    double *d_sit = nullptr, *d_sgrad = nullptr;
+    if (params->estimation == 2 && Nt > 0) {
+        if (ctx->icp_e.ensure(al(sizeof(double) * (size_t)Nt) + al(sizeof(double) * 3 * (size_t)Nt))) return -102;
+        d_sit = (double*)ctx->icp_e.ptr;
+        d_sgrad = (double*)((char*)ctx->icp_e.ptr + al(sizeof(double) * (size_t)Nt));
+        if (max_nt > 0) {
+            icp_gather_color_kernel<<<dim3(cdiv(max_nt, 256), n_pairs), 256, 0, st>>>(d_tgt_colors, d_tgt_color_grad, d_pairs, d_sidx,
+                                                                                      d_sit, d_sgrad);
+            B2R_LAUNCH_CHECK(ctx);
+        }
+    }
+
     // ---- iterate: max_iteration + 1 evaluations, no host sync in between ----
     IcpArgs A;
+    A.src_col = d_src_colors; A.s_it = d_sit; A.s_grad = d_sgrad;
+    A.sqrt_lg = sqrt(params->lambda_geometric); A.sqrt_lp = sqrt(1.0 - params->lambda_geometric);
     A.src = d_src_points; A.s_pts = d_spts; A.s_nrm = d_snrm; A.s_idx = d_sidx; A.keys = d_keys; A.starts = d_starts;
     A.counts = d_counts; A.pairs = d_pairs; A.states = d_states; A.partials = d_partials; A.partial_stride = max_blocks;
     A.corr = d_corr; A.r2 = params->max_correspondence_distance * params->max_correspondence_distance;
     A.rel_fitness = params->relative_fitness; A.rel_rmse = params->relative_rmse;
     A.max_iter = params->max_iteration < 0 ? 0 : params->max_iteration; A.estimation = params->estimation;
     for (int it = 0; it <= A.max_iter; ++it) {
-        icp_iterate_kernel<<<dim3(max_blocks, n_pairs), ICP_THREADS, 0, st>>>(A);
+        if (A.estimation == 2) icp_iterate_kernel<2><<<dim3(max_blocks, n_pairs), ICP_THREADS, 0, st>>>(A);
+        else if (A.estimation == 1) icp_iterate_kernel<1><<<dim3(max_blocks, n_pairs), ICP_THREADS, 0, st>>>(A);
+        else icp_iterate_kernel<0><<<dim3(max_blocks, n_pairs), ICP_THREADS, 0, st>>>(A);
         B2R_LAUNCH_CHECK(ctx);
     }
     B2R_CUDA(cudaMemcpyAsync(hs.data(), d_states, sizeof(IcpState) * n_pairs, cudaMemcpyDeviceToHost, st));

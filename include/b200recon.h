@@ -174,6 +174,45 @@ int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_points, const i
                   const double* h_init /* [n_pairs*16] */, const b2r_icp_params* params,
                   b2r_icp_result* h_results, int32_t* d_corr, void* stream);
 
+/* ---- point-cloud preprocessing around ICP ---------------------- */
+/* Neighbour search modes: O3D geometry.KDTreeSearchParamKNN(knn) / KDTreeSearchParamHybrid(radius, max_nn)
+ * (stitcher.py:63,69).  Searches are exact (uniform-grid hash, ring walk with distance pruning); neighbours are
+ * ordered by (squared distance, index) like a k-d tree result, the query point included; max_nn <= 128. */
+#define B2R_SEARCH_KNN 0
+#define B2R_SEARCH_HYBRID 2
+
+/* O3D PointCloud.voxel_down_sample(voxel_size) -- stitcher.py:58,151.  Cell = floor((p - (min_bound -
+ * voxel_size/2)) / voxel_size); outputs the per-cell means of points / normals / colours (d_normals, d_colors
+ * and their outputs may be NULL), cells ordered by their first point index (Open3D: unordered_map order).
+ * Output buffers hold up to n points.  Blocking: *h_n_out = number of cells.
+ * Errors: voxel_size <= 0 ("[VoxelDownSample] voxel_size <= 0."), voxel_size too small for the extent. */
+int b2r_voxel_down_sample(b2r_ctx* ctx, const double* d_points, const double* d_normals, const double* d_colors,
+                          int64_t n, double voxel_size, double* d_out_points, double* d_out_normals,
+                          double* d_out_colors, int64_t* h_n_out, void* stream);
+
+/* O3D PointCloud.estimate_normals(search_param, fast_normal_computation=True) -- stitcher.py:61-63.
+ * Covariance of the neighbours (cumulants in search order) -> eigenvector of the smallest eigenvalue
+ * (closed-form FastEigen3x3); fewer than 3 neighbours or a zero vector -> (0,0,1); d_prev_normals (optional):
+ * pre-existing normals the result is flipped to agree with.  d_out may alias d_prev_normals. */
+int b2r_estimate_normals(b2r_ctx* ctx, const double* d_points, int64_t n, int search_mode, double radius,
+                         int max_nn, const double* d_prev_normals, double* d_out_normals, void* stream);
+
+/* O3D PointCloud.remove_statistical_outlier(nb_neighbors, std_ratio) -- stitcher.py:158-159.  Mean distance to
+ * the nb_neighbors nearest points (query included) per point; keeps points with 0 < mean < cloud mean +
+ * std_ratio * sample std.  d_indices_out: int64 [n], kept indices ascending.  Blocking: *h_n_out = kept. */
+int b2r_statistical_outlier(b2r_ctx* ctx, const double* d_points, int64_t n, int nb_neighbors, double std_ratio,
+                            int64_t* d_indices_out, int64_t* h_n_out, void* stream);
+
+/* O3D InitializePointCloudForColoredICP(target, KDTreeSearchParamHybrid(radius, max_nn)) -- the per-point colour
+ * gradient registration_colored_icp (stitcher.py:94-102) precomputes on the target.  d_grad_out: double [n,3]. */
+int b2r_color_gradient(b2r_ctx* ctx, const double* d_points, const double* d_normals, const double* d_colors,
+                       int64_t n, double radius, int max_nn, double* d_grad_out, void* stream);
+
+/* Neighbour lists of the search above, for tests: d_idx_out int32 [n_query, k] (-1 padded), d_d2_out double
+ * [n_query, k].  Queries must lie inside the cloud's bounding box (they are cloud points in every caller). */
+int b2r_knn_search(b2r_ctx* ctx, const double* d_points, int64_t n, const double* d_queries, int64_t n_query,
+                   int search_mode, double radius, int k, int32_t* d_idx_out, double* d_d2_out, void* stream);
+
 /* ---- synthetic frame source (replaces bullet_camera.py:48-85 / data_recorder.py:104-121) -- */
 typedef struct b2r_scene {
     float c2w[12];            /* camera->world 3x4 row-major */

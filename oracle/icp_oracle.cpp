@@ -166,17 +166,14 @@ void evaluate(const std::vector<double>& src, const orc::KDTree& tree, double ma
 
 }  // namespace
 
-extern "C" {
-
-// kind: 0 = PointToPoint (Umeyama, no scaling), 1 = PointToPlane.
-// corr_out: int32[Ns] (target index per source point or -1) may be NULL.
-// Returns 0, or <0 on the errors Open3D raises (max_dist<=0 -> -1, p2plane without normals -> -2).
-int orc_registration_icp(const double* src_pts, int64_t Ns, const double* tgt_pts, const double* tgt_normals,
-                         int64_t Nt, double max_dist, const double* init, int kind, double rel_fitness,
-                         double rel_rmse, int max_iter, double* T_out, double* fitness, double* rmse,
-                         int32_t* corr_out, int64_t* n_corr, int* iterations) {
+static int run_icp(const double* src_pts, int64_t Ns, const double* tgt_pts, const double* tgt_normals,
+                   int64_t Nt, double max_dist, const double* init, int kind, double rel_fitness,
+                   double rel_rmse, int max_iter, double* T_out, double* fitness, double* rmse,
+                   int32_t* corr_out, int64_t* n_corr, int* iterations, const double* src_col,
+                   const double* tgt_col, const double* tgt_grad, double lambda_geometric) {
     if (max_dist <= 0) return -1;
-    if (kind == 1 && !tgt_normals) return -2;
+    if (kind >= 1 && !tgt_normals) return -2;
+    if (kind == 2 && !(src_col && tgt_col && tgt_grad)) return -3;
     orc::KDTree tree; tree.build(tgt_pts, Nt);
     double T[16];
     std::memcpy(T, init, sizeof(T));
@@ -189,7 +186,40 @@ int orc_registration_icp(const double* src_pts, int64_t Ns, const double* tgt_pt
         double upd[16];
         for (int i = 0; i < 16; ++i) upd[i] = (i % 5 == 0);
         if (res.K > 0) {
-            if (kind == 1) {
+            if (kind == 2) {
+                // TransformationEstimationForColoredICP::ComputeTransformation (A.6): two residuals per
+                // correspondence, geometric sqrt(lambda) (vs-vt).nt and photometric sqrt(1-lambda) (is - is0_proj).
+                double JTJ[36] = {0}, JTr[6] = {0};
+                const double sg = std::sqrt(lambda_geometric), sp = std::sqrt(1.0 - lambda_geometric);
+                for (int64_t i = 0; i < Ns; ++i) {
+                    const int j = res.corr[i]; if (j < 0) continue;
+                    const double* vs = &pcd[i * 3]; const double* vt = &tgt_pts[(int64_t)j * 3];
+                    const double* nt = &tgt_normals[(int64_t)j * 3];
+                    const double* dit = &tgt_grad[(int64_t)j * 3];
+                    const double dn = (vs[0] - vt[0]) * nt[0] + (vs[1] - vt[1]) * nt[1] + (vs[2] - vt[2]) * nt[2];
+                    double J[2][6], r[2];
+                    const double cr[3] = {vs[1] * nt[2] - vs[2] * nt[1], vs[2] * nt[0] - vs[0] * nt[2], vs[0] * nt[1] - vs[1] * nt[0]};
+                    for (int k = 0; k < 3; ++k) { J[0][k] = sg * cr[k]; J[0][3 + k] = sg * nt[k]; }
+                    r[0] = sg * dn;
+                    const double vp[3] = {vs[0] - dn * nt[0], vs[1] - dn * nt[1], vs[2] - dn * nt[2]};
+                    const double is = (src_col[i * 3] + src_col[i * 3 + 1] + src_col[i * 3 + 2]) / 3.0;
+                    const double it = (tgt_col[(int64_t)j * 3] + tgt_col[(int64_t)j * 3 + 1] + tgt_col[(int64_t)j * 3 + 2]) / 3.0;
+                    const double is0 = (dit[0] * (vp[0] - vt[0]) + dit[1] * (vp[1] - vt[1]) + dit[2] * (vp[2] - vt[2])) + it;
+                    const double M[9] = {1.0 - nt[0] * nt[0], -nt[0] * nt[1], -nt[0] * nt[2], -nt[0] * nt[1], 1.0 - nt[1] * nt[1],
+                                         -nt[1] * nt[2], -nt[0] * nt[2], -nt[1] * nt[2], 1.0 - nt[2] * nt[2]};
+                    double dm[3];
+                    for (int c = 0; c < 3; ++c) dm[c] = (-dit[0]) * M[c] + (-dit[1]) * M[3 + c] + (-dit[2]) * M[6 + c];
+                    const double cm[3] = {vs[1] * dm[2] - vs[2] * dm[1], vs[2] * dm[0] - vs[0] * dm[2], vs[0] * dm[1] - vs[1] * dm[0]};
+                    for (int k = 0; k < 3; ++k) { J[1][k] = sp * cm[k]; J[1][3 + k] = sp * dm[k]; }
+                    r[1] = sp * (is - is0);
+                    for (int e = 0; e < 2; ++e)
+                        for (int a = 0; a < 6; ++a) { for (int b = 0; b < 6; ++b) JTJ[a * 6 + b] += J[e][a] * J[e][b]; JTr[a] += J[e][a] * r[e]; }
+                }
+                double nb[6], x[6];
+                for (int a = 0; a < 6; ++a) nb[a] = -JTr[a];
+                ldlt_solve(6, JTJ, nb, x);
+                vec6_to_mat4(x, upd);
+            } else if (kind == 1) {
                 double JTJ[36] = {0}, JTr[6] = {0};
                 // (Open3D: OpenMP with private partials; sum order is unpinned -> serial here.)
                 for (int64_t i = 0; i < Ns; ++i) {
@@ -241,6 +271,30 @@ int orc_registration_icp(const double* src_pts, int64_t Ns, const double* tgt_pt
     if (corr_out) std::memcpy(corr_out, res.corr.data(), sizeof(int32_t) * (size_t)Ns);
     if (iterations) *iterations = it;
     return 0;
+}
+
+extern "C" {
+
+// kind: 0 = PointToPoint (Umeyama, no scaling), 1 = PointToPlane.
+// corr_out: int32[Ns] (target index per source point or -1) may be NULL.
+// Returns 0, or <0 on the errors Open3D raises (max_dist<=0 -> -1, p2plane without normals -> -2).
+int orc_registration_icp(const double* src_pts, int64_t Ns, const double* tgt_pts, const double* tgt_normals,
+                         int64_t Nt, double max_dist, const double* init, int kind, double rel_fitness,
+                         double rel_rmse, int max_iter, double* T_out, double* fitness, double* rmse,
+                         int32_t* corr_out, int64_t* n_corr, int* iterations) {
+    return run_icp(src_pts, Ns, tgt_pts, tgt_normals, Nt, max_dist, init, kind, rel_fitness, rel_rmse, max_iter, T_out,
+                   fitness, rmse, corr_out, n_corr, iterations, nullptr, nullptr, nullptr, 0.968);
+}
+
+// RegistrationColoredICP (stitcher.py:94-102; A.6) once the target's colour gradient is known
+// (orc_color_gradient with radius = 2 * max_dist, max_nn = 30).  -3: colours / gradient missing.
+int orc_registration_colored_icp(const double* src_pts, const double* src_col, int64_t Ns, const double* tgt_pts,
+                                 const double* tgt_normals, const double* tgt_col, const double* tgt_grad, int64_t Nt,
+                                 double max_dist, const double* init, double lambda_geometric, double rel_fitness,
+                                 double rel_rmse, int max_iter, double* T_out, double* fitness, double* rmse,
+                                 int32_t* corr_out, int64_t* n_corr, int* iterations) {
+    return run_icp(src_pts, Ns, tgt_pts, tgt_normals, Nt, max_dist, init, 2, rel_fitness, rel_rmse, max_iter, T_out,
+                   fitness, rmse, corr_out, n_corr, iterations, src_col, tgt_col, tgt_grad, lambda_geometric);
 }
 
 // Exposed for cross-checks in tests (vs scipy.spatial.cKDTree).

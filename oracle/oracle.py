@@ -59,6 +59,19 @@ def lib():
                                            C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int)]
         L.orc_nearest.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_double, C.c_void_p, C.c_void_p]
         L.orc_raycast_scene.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_registration_colored_icp.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                   C.c_void_p, C.c_int64, C.c_double, c_dp, C.c_double, C.c_double,
+                                                   C.c_double, C.c_int, c_dp, c_dp, c_dp, C.c_void_p,
+                                                   C.POINTER(C.c_int64), C.POINTER(C.c_int)]
+        L.orc_voxel_down_sample.restype = C.c_int64
+        L.orc_voxel_down_sample.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_void_p,
+                                            C.c_void_p, C.c_void_p]
+        L.orc_estimate_normals.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_statistical_outlier.restype = C.c_int64
+        L.orc_statistical_outlier.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_void_p, C.c_void_p]
+        L.orc_color_gradient.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_int, C.c_void_p]
+        L.orc_knn.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_int, C.c_void_p,
+                              C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -205,6 +218,83 @@ def registration_icp(src, tgt, tgt_normals, max_dist, init=None, kind=1, rel_fit
         raise RuntimeError("oracle registration_icp error %d" % rc)
     return dict(transformation=T, fitness=fit.value, inlier_rmse=rmse.value, corr=corr, n_corr=nc.value,
                 iterations=it.value)
+
+
+def registration_colored_icp(src, src_col, tgt, tgt_normals, tgt_col, max_dist, init=None, lambda_geometric=0.968,
+                             rel_fitness=1e-6, rel_rmse=1e-6, max_iter=30, tgt_grad=None):
+    """A.6: colour gradient of the target (Hybrid(2*max_dist, 30)) + two-residual ICP.  Returns dict."""
+    a = lambda v: np.ascontiguousarray(v, np.float64)
+    src, src_col, tgt, tgt_normals, tgt_col = a(src), a(src_col), a(tgt), a(tgt_normals), a(tgt_col)
+    if tgt_grad is None:
+        tgt_grad = color_gradient(tgt, tgt_normals, tgt_col, 2.0 * max_dist, 30)
+    tgt_grad = a(tgt_grad)
+    init = a(np.eye(4) if init is None else init)
+    T = np.empty((4, 4), np.float64)
+    fit, rmse = C.c_double(0), C.c_double(0)
+    corr = np.empty((len(src),), np.int32)
+    nc, it = C.c_int64(0), C.c_int(0)
+    rc = lib().orc_registration_colored_icp(_vp(src), _vp(src_col), len(src), _vp(tgt), _vp(tgt_normals), _vp(tgt_col),
+                                            _vp(tgt_grad), len(tgt), max_dist, _dp(init), lambda_geometric, rel_fitness,
+                                            rel_rmse, max_iter, _dp(T), C.byref(fit), C.byref(rmse), _vp(corr),
+                                            C.byref(nc), C.byref(it))
+    if rc != 0:
+        raise RuntimeError("oracle registration_colored_icp error %d" % rc)
+    return dict(transformation=T, fitness=fit.value, inlier_rmse=rmse.value, corr=corr, n_corr=nc.value,
+                iterations=it.value, color_gradient=tgt_grad)
+
+
+# ---------------------------------------------------------------------------------- point-cloud preprocessing
+SEARCH_KNN, SEARCH_RADIUS, SEARCH_HYBRID = 0, 1, 2
+
+
+def voxel_down_sample(pts, voxel_size, normals=None, colors=None):
+    """A.7 -> (points, normals|None, colors|None); cells in order of their first point index."""
+    a = lambda v: None if v is None else np.ascontiguousarray(v, np.float64)
+    pts, normals, colors = a(pts), a(normals), a(colors)
+    n = len(pts)
+    op = np.empty((n, 3))
+    on = np.empty((n, 3)) if normals is not None else None
+    oc = np.empty((n, 3)) if colors is not None else None
+    m = lib().orc_voxel_down_sample(_vp(pts), _vp(normals), _vp(colors), n, float(voxel_size), _vp(op), _vp(on), _vp(oc))
+    if m < 0:
+        raise RuntimeError("[VoxelDownSample] voxel_size <= 0.")
+    return op[:m].copy(), None if on is None else on[:m].copy(), None if oc is None else oc[:m].copy()
+
+
+def estimate_normals(pts, mode=SEARCH_HYBRID, radius=0.1, max_nn=30, prev=None):
+    """A.8 (fast_normal_computation=True)."""
+    pts = np.ascontiguousarray(pts, np.float64)
+    prev = None if prev is None else np.ascontiguousarray(prev, np.float64)
+    out = np.empty_like(pts)
+    lib().orc_estimate_normals(_vp(pts), len(pts), mode, float(radius), int(max_nn), _vp(prev), _vp(out))
+    return out
+
+
+def statistical_outlier(pts, nb_neighbors, std_ratio):
+    """A.9 -> (kept indices int64 ascending, per-point mean neighbour distance)."""
+    pts = np.ascontiguousarray(pts, np.float64)
+    idx = np.empty((len(pts),), np.int64)
+    avg = np.empty((len(pts),), np.float64)
+    m = lib().orc_statistical_outlier(_vp(pts), len(pts), int(nb_neighbors), float(std_ratio), _vp(idx), _vp(avg))
+    return idx[:m].copy(), avg
+
+
+def color_gradient(pts, normals, colors, radius, max_nn=30):
+    """A.6 InitializePointCloudForColoredICP."""
+    a = lambda v: np.ascontiguousarray(v, np.float64)
+    pts, normals, colors = a(pts), a(normals), a(colors)
+    g = np.empty_like(pts)
+    lib().orc_color_gradient(_vp(pts), _vp(normals), _vp(colors), len(pts), float(radius), int(max_nn), _vp(g))
+    return g
+
+
+def knn(pts, q, mode, radius, k):
+    pts = np.ascontiguousarray(pts, np.float64)
+    q = np.ascontiguousarray(q, np.float64)
+    idx = np.empty((len(q), k), np.int32)
+    d2 = np.empty((len(q), k), np.float64)
+    lib().orc_knn(_vp(pts), len(pts), _vp(q), len(q), mode, float(radius), k, _vp(idx), _vp(d2))
+    return idx, d2
 
 
 def nearest(tgt, q, max_dist):
