@@ -526,45 +526,70 @@ __global__ void __launch_bounds__(256) cl_first_flag_kernel(const uint32_t* __re
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) flag[i] = (first[slot_of[i]] == (uint32_t)i) ? 1u : 0u;
 }
-__global__ void __launch_bounds__(256) cl_cell_pos_kernel(const uint32_t* __restrict__ slot_of, const uint32_t* __restrict__ flag,
-                                                          const uint32_t* __restrict__ pos, long long n, uint32_t* __restrict__ cell_of_slot) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n && flag[i]) cell_of_slot[slot_of[i]] = pos[i];
-}
-// AccumulatedPoint::AddPoint: per-cell sums of point / normal (NaN normals skipped) / colour.  float64 atomics:
-// the sum ORDER differs from Open3D's sequential loop (and from run to run) by rounding only.
-__global__ void __launch_bounds__(256) cl_accumulate_kernel(const double* __restrict__ pts, const double* __restrict__ nrm,
-                                                            const double* __restrict__ col, long long n,
-                                                            const uint32_t* __restrict__ slot_of,
-                                                            const uint32_t* __restrict__ cell_of_slot, double* __restrict__ acc) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    double* a = acc + (long long)cell_of_slot[slot_of[i]] * 9;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) atomicAdd(a + k, pts[i * 3 + k]);
-    if (nrm) {
-        const double x = nrm[i * 3], y = nrm[i * 3 + 1], z = nrm[i * 3 + 2];
-        if (!(isnan(x) || isnan(y) || isnan(z))) { atomicAdd(a + 3, x); atomicAdd(a + 4, y); atomicAdd(a + 5, z); }
+// The scatter leaves every cell's index list in arbitrary order; Open3D adds the points of a cell in ascending
+// index order (one sequential loop over the cloud), and float64 addition is not associative -- so each list is
+// sorted first (one warp per hash slot, ascending-only bitonic network over the slot's segment, virtual +inf
+// padding up to the next power of two) and then summed sequentially by one thread: bit-identical means.
+__global__ void __launch_bounds__(128) cl_sort_cells_kernel(const uint32_t* __restrict__ starts, const uint32_t* __restrict__ counts,
+                                                            unsigned int n_slots, int32_t* s_idx) {
+    const unsigned int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (slot >= n_slots) return;
+    const uint32_t m = counts[slot];
+    if (m < 2) return;
+    int32_t* a = s_idx + starts[slot];
+    const int lane = threadIdx.x & 31;
+    uint32_t p2 = 2;
+    while (p2 < m) p2 <<= 1;
+    for (uint32_t k = 2; k <= p2; k <<= 1) {
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            const bool flip = (j == (k >> 1));           // first stage of a merge mirrors, the rest are half-cleaners
+            for (uint32_t t = lane; t < (p2 >> 1); t += 32) {
+                // t-th compare-exchange of this stage: lo has bit j clear
+                const uint32_t lo = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const uint32_t hi = flip ? (lo ^ (k - 1)) : (lo | j);
+                if (hi < m) {                            // (lo < hi always; an out-of-range hi is +inf: no exchange)
+                    const int32_t x = a[lo], y = a[hi];
+                    if (x > y) { a[lo] = y; a[hi] = x; }
+                }
+            }
+            __syncwarp();
+        }
     }
-    if (col) {
-#pragma unroll
-        for (int k = 0; k < 3; ++k) atomicAdd(a + 6 + k, col[i * 3 + k]);
-    }
 }
-__global__ void __launch_bounds__(256) cl_average_kernel(const uint32_t* __restrict__ slot_of, const uint32_t* __restrict__ flag,
-                                                         const uint32_t* __restrict__ pos, const uint32_t* __restrict__ counts,
-                                                         const double* __restrict__ acc, long long n, double* __restrict__ out_p,
-                                                         double* __restrict__ out_n, double* __restrict__ out_c) {
+
+// AccumulatedPoint::AddPoint / GetAverage*: sequential sums in ascending point order (NaN normals skipped),
+// divided by the cell's point count.  One thread per cell (the thread of the cell's first point).
+__global__ void __launch_bounds__(128) cl_cell_mean_kernel(const double* __restrict__ pts, const double* __restrict__ nrm,
+                                                           const double* __restrict__ col, long long n,
+                                                           const uint32_t* __restrict__ slot_of, const uint32_t* __restrict__ flag,
+                                                           const uint32_t* __restrict__ pos, const uint32_t* __restrict__ starts,
+                                                           const uint32_t* __restrict__ counts, const int32_t* __restrict__ s_idx,
+                                                           double* __restrict__ out_p, double* __restrict__ out_n,
+                                                           double* __restrict__ out_c) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || !flag[i]) return;
+    const uint32_t slot = slot_of[i], st = starts[slot], m = counts[slot];
+    double sp[3] = {0.0, 0.0, 0.0}, sn[3] = {0.0, 0.0, 0.0}, sc[3] = {0.0, 0.0, 0.0};
+    for (uint32_t e = 0; e < m; ++e) {
+        const long long j = s_idx[st + e];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) sp[k] += pts[j * 3 + k];
+        if (nrm) {
+            const double x = nrm[j * 3], y = nrm[j * 3 + 1], z = nrm[j * 3 + 2];
+            if (!(isnan(x) || isnan(y) || isnan(z))) { sn[0] += x; sn[1] += y; sn[2] += z; }
+        }
+        if (col) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) sc[k] += col[j * 3 + k];
+        }
+    }
     const long long c = pos[i];
-    const double d = (double)counts[slot_of[i]];
-    const double* a = acc + c * 9;
+    const double d = (double)m;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        out_p[c * 3 + k] = a[k] / d;
-        if (out_n) out_n[c * 3 + k] = a[3 + k] / d;
-        if (out_c) out_c[c * 3 + k] = a[6 + k] / d;
+        out_p[c * 3 + k] = sp[k] / d;
+        if (out_n) out_n[c * 3 + k] = sn[k] / d;
+        if (out_c) out_c[c * 3 + k] = sc[k] / d;
     }
 }
 
@@ -620,7 +645,7 @@ static int build_grid(b2r_ctx* ctx, const double* d_pts, int64_t n, double voxel
     B2R_LAUNCH_CHECK(ctx);
     cl_grid_setup_kernel<<<1, 1, 0, st>>>(B.d_grid, B.d_bb, n, voxel_size, radius, k);
     B2R_LAUNCH_CHECK(ctx);
-    cl_insert_kernel<<<cdiv(n, 256), 256, 0, st>>>(d_pts, n, B.d_grid, B.keys, B.counts, sorted ? nullptr : B.first, B.slot_of,
+    cl_insert_kernel<<<cdiv(n, 256), 256, 0, st>>>(d_pts, n, B.d_grid, B.keys, B.counts, B.first, B.slot_of,
                                                    B.tab_mask);
     B2R_LAUNCH_CHECK(ctx);
     if (sorted) {
@@ -661,26 +686,21 @@ int b2r_voxel_down_sample(b2r_ctx* ctx, const double* d_points, const double* d_
     B2R_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t st = S(stream);
     GridBuf B;
-    if (int rc = build_grid(ctx, d_points, n, voxel_size, 0.0, 0, false, B, st)) return rc;
-    // flags / positions / cell ids / accumulators
-    const size_t sz_n = al256(sizeof(uint32_t) * (size_t)n), sz_t = al256(sizeof(uint32_t) * ((size_t)B.tab_mask + 1));
-    if (ctx->cl_c.ensure(2 * sz_n + sz_t + al256(sizeof(double) * 9 * (size_t)n))) return -102;
+    if (int rc = build_grid(ctx, d_points, n, voxel_size, 0.0, 0, true, B, st)) return rc;
+    const size_t sz_n = al256(sizeof(uint32_t) * (size_t)n);
+    if (ctx->cl_c.ensure(2 * sz_n)) return -102;
     uint32_t* flag = (uint32_t*)ctx->cl_c.ptr;
     uint32_t* pos = (uint32_t*)((char*)ctx->cl_c.ptr + sz_n);
-    uint32_t* cell_of_slot = (uint32_t*)((char*)ctx->cl_c.ptr + 2 * sz_n);
-    double* acc = (double*)((char*)ctx->cl_c.ptr + 2 * sz_n + sz_t);
     unsigned long long* d_total = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64;
-    const int g = cdiv(n, 256);
-    cl_first_flag_kernel<<<g, 256, 0, st>>>(B.slot_of, B.first, n, flag);
+    const unsigned int n_slots = B.tab_mask + 1;
+    cl_sort_cells_kernel<<<cdiv(n_slots, 4), 128, 0, st>>>(B.starts, B.counts, n_slots, B.s_idx);
+    B2R_LAUNCH_CHECK(ctx);
+    cl_first_flag_kernel<<<cdiv(n, 256), 256, 0, st>>>(B.slot_of, B.first, n, flag);
     B2R_LAUNCH_CHECK(ctx);
     if (int rc = scan_exclusive_u32(ctx, flag, pos, n, d_total, st)) return rc;
-    cl_cell_pos_kernel<<<g, 256, 0, st>>>(B.slot_of, flag, pos, n, cell_of_slot);
-    B2R_LAUNCH_CHECK(ctx);
-    B2R_CUDA(cudaMemsetAsync(acc, 0, sizeof(double) * 9 * (size_t)n, st));
-    cl_accumulate_kernel<<<g, 256, 0, st>>>(d_points, d_normals, d_colors, n, B.slot_of, cell_of_slot, acc);
-    B2R_LAUNCH_CHECK(ctx);
-    cl_average_kernel<<<g, 256, 0, st>>>(B.slot_of, flag, pos, B.counts, acc, n, d_out_points, d_normals ? d_out_normals : nullptr,
-                                         d_colors ? d_out_colors : nullptr);
+    cl_cell_mean_kernel<<<cdiv(n, 128), 128, 0, st>>>(d_points, d_normals, d_colors, n, B.slot_of, flag, pos, B.starts, B.counts,
+                                                      B.s_idx, d_out_points, d_normals ? d_out_normals : nullptr,
+                                                      d_colors ? d_out_colors : nullptr);
     B2R_LAUNCH_CHECK(ctx);
     CloudGrid hg;
     B2R_CUDA(cudaMemcpyAsync(ctx->pinned, d_total, 8, cudaMemcpyDeviceToHost, st));

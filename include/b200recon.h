@@ -183,7 +183,8 @@ int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_points, const i
 
 /* O3D PointCloud.voxel_down_sample(voxel_size) -- stitcher.py:58,151.  Cell = floor((p - (min_bound -
  * voxel_size/2)) / voxel_size); outputs the per-cell means of points / normals / colours (d_normals, d_colors
- * and their outputs may be NULL), cells ordered by their first point index (Open3D: unordered_map order).
+ * and their outputs may be NULL), cells ordered by their first point index (Open3D: unordered_map order).  The sums
+ * run in ascending point order per cell, like Open3D's sequential loop: the means are bit-identical to it.
  * Output buffers hold up to n points.  Blocking: *h_n_out = number of cells.
  * Errors: voxel_size <= 0 ("[VoxelDownSample] voxel_size <= 0."), voxel_size too small for the extent. */
 int b2r_voxel_down_sample(b2r_ctx* ctx, const double* d_points, const double* d_normals, const double* d_colors,

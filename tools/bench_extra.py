@@ -1,0 +1,145 @@
+#!/usr/bin/env python3
+"""Secondary measurements of the path: batched ICP pairs/s (BASELINE config 4), marching-cubes /
+point extraction time, and the point-cloud preprocessing rows (f1/f2) at full-frame size.  CUDA-event timing.
+
+    python tools/bench_extra.py [--pairs 64] [--res 512] [--frames 64]
+Prints one JSON object.  bench.py imports `icp_bench` / `mesh_bench` for the extra keys of its JSON line."""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for _p in (ROOT, os.path.join(ROOT, "3d-reconstruction-planning_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+
+def _ev():
+    import torch
+    return torch.cuda.Event(enable_timing=True)
+
+
+def timed(fn, reps=1):
+    import torch
+    torch.cuda.synchronize()
+    e0, e1 = _ev(), _ev()
+    e0.record()
+    for _ in range(reps):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps, out
+
+
+def make_clouds(n_frames, radius=0.5, K=None, with_normals=True, normal_radius=0.004):
+    """Back-projected full-frame clouds (~300 k points at 640x480) of consecutive orbit frames, moved to the
+    WORLD frame by the known pose so that consecutive clouds overlap; normals by estimate_normals."""
+    import b200recon as o3d
+    from b200recon import synthetic as syn
+    K = K or syn.D435_640x480
+    intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], K["fx"], K["fy"], K["cx"], K["cy"])
+    poses = syn.orbit_poses(64, radius=radius, elevation_deg=30.0)[:n_frames]
+    clouds = []
+    t_norm = 0.0
+    for p in poses:
+        d16, rgb = syn.render_frame(p, K)
+        rgbd = o3d.geometry.RGBDImage.create_from_color_and_depth(o3d.geometry.Image(rgb.cpu().numpy()),
+                                                                  o3d.geometry.Image(d16.cpu().numpy()),
+                                                                  convert_rgb_to_intensity=False)
+        pc = o3d.geometry.PointCloud.create_from_rgbd_image(rgbd, intr, syn.extrinsic_from_pose(p))
+        if with_normals:
+            ms, _ = timed(lambda: pc.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(normal_radius, 30)))
+            t_norm += ms
+        clouds.append(pc)
+    return clouds, t_norm / max(1, len(clouds))
+
+
+def icp_bench(n_pairs=64, max_dist=0.004, rank=0, world=1, reps=1):
+    """BASELINE config 4: n_pairs frame pairs x ~300 k points, point-to-plane, criteria (1e-6, 1e-6, 30), pair p on
+    GPU p % world.  The source of pair p is cloud p perturbed by a small known SE(3); the target is cloud p+1 of the orbit.
+    Returns dict(pairs_per_s (this rank), ms, iterations, fitness...)."""
+    import b200recon as o3d
+    reg = o3d.pipelines.registration
+    mine = [p for p in range(n_pairs) if p % world == rank]
+    base, t_norm = make_clouds(min(9, len(mine) + 1))
+    src, tgt, inits = [], [], []
+    ca, sa = np.cos(0.004), np.sin(0.004)
+    T0 = np.array([[ca, -sa, 0, 0.001], [sa, ca, 0, -0.0008], [0, 0, 1, 0.0005], [0, 0, 0, 1.0]])
+    for i, p in enumerate(mine):
+        a = base[i % (len(base) - 1)]
+        b = base[i % (len(base) - 1) + 1]
+        s = a.clone()
+        s.transform(T0)
+        src.append(s)
+        tgt.append(b)
+        inits.append(np.eye(4))
+    est = reg.TransformationEstimationPointToPlane()
+    crit = reg.ICPConvergenceCriteria(1e-6, 1e-6, 30)
+    run = lambda: reg.registration_icp_batch(src, tgt, max_dist, inits, est, crit, with_correspondences=False)
+    run()   # warm-up (scratch allocation)
+    ms, res = timed(run, reps)
+    npts = float(np.mean([len(s) for s in src]))
+    return {"pairs": len(mine), "ms": ms, "pairs_per_s": len(mine) / (ms * 1e-3), "points_per_cloud": npts,
+            "max_correspondence_distance": max_dist, "estimation": "point_to_plane",
+            "iterations_mean": float(np.mean([r.iterations for r in res])),
+            "fitness_mean": float(np.mean([r.fitness for r in res])),
+            "rmse_mean": float(np.mean([r.inlier_rmse for r in res])),
+            "estimate_normals_ms_per_cloud": t_norm}
+
+
+def mesh_bench(vol, reps=2):
+    """extract_triangle_mesh / extract_point_cloud of an integrated volume (device arrays, no host copy)."""
+    vol.extract_triangle_mesh_device()
+    ms_m, m = timed(lambda: vol.extract_triangle_mesh_device(), reps)
+    ms_p, p = timed(lambda: vol.extract_point_cloud_device(), reps)
+    return {"mesh_ms": ms_m, "vertices": int(m[0].shape[0]), "triangles": int(m[1].shape[0]),
+            "point_cloud_ms": ms_p, "points": int(p[0].shape[0])}
+
+
+def preprocess_bench():
+    import b200recon as o3d
+    clouds, _ = make_clouds(2, with_normals=False)
+    pc = clouds[0]
+    out = {"points": len(pc)}
+    out["voxel_down_sample_20mm_ms"], d = timed(lambda: pc.voxel_down_sample(0.02), 3)
+    out["voxel_down_sample_2mm_ms"], d2 = timed(lambda: pc.voxel_down_sample(0.002), 3)
+    out["cells_20mm"], out["cells_2mm"] = len(d), len(d2)
+    out["estimate_normals_hybrid_4mm_30_ms"], _ = timed(lambda: pc.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(0.004, 30)), 2)
+    out["remove_statistical_outlier_20_ms"], _ = timed(lambda: pc.remove_statistical_outlier(20, 2.0), 2)
+    out["estimate_normals_down2mm_hybrid_40mm_30_ms"], _ = timed(lambda: d2.estimate_normals(o3d.geometry.KDTreeSearchParamHybrid(0.04, 30)), 2)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--pairs", type=int, default=64)
+    ap.add_argument("--res", type=int, default=512)
+    ap.add_argument("--frames", type=int, default=64)
+    args = ap.parse_args()
+    import b200recon as o3d
+    from b200recon import synthetic as syn
+    out = {}
+    t0 = time.time()
+    out["preprocess"] = preprocess_bench()
+    out["icp_tight"] = icp_bench(args.pairs, 0.004)
+    out["icp_wide"] = icp_bench(min(args.pairs, 8), 0.05)
+    K = syn.D435_640x480
+    L = args.res * 0.002
+    intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], K["fx"], K["fy"], K["cx"], K["cy"])
+    vol = o3d.pipelines.integration.UniformTSDFVolume(L, args.res, 0.01, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
+                                                      syn.volume_origin(L))
+    import torch
+    for p in syn.orbit_poses(args.frames, radius=0.5 if args.res <= 512 else 0.9):
+        d16, rgb = syn.render_frame(p, K)
+        vol.integrate_host(d16.cpu().numpy(), rgb.cpu().numpy(), intr, syn.extrinsic_from_pose(p))
+    out["mesh_%d" % args.res] = mesh_bench(vol)
+    out["wall_s"] = time.time() - t0
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
