@@ -161,6 +161,33 @@ def run_cpu(workload, steps, warmup, K, budget_s=25.0):
     return fps, upd / dt, n, sample, dt
 
 
+def run_cpu_icp(K, max_dist=0.004):
+    """One pair of BASELINE config 4 on the oracle (exact k-d tree + OpenMP, Open3D's parallelisation): two
+    consecutive orbit frames back-projected to ~300 k points each, analytic-free normals from the oracle's
+    estimate_normals; returns pairs/s on the host cores."""
+    from b200recon import synthetic as syn
+    from oracle import oracle as orc
+    kt = (K["fx"], K["fy"], K["cx"], K["cy"])
+    poses = syn.orbit_poses(64, radius=0.5, elevation_deg=30.0)[:2]
+    clouds = []
+    for p in poses:
+        d16, rgb = orc.raycast_scene(p, kt, K["width"], K["height"])
+        P, _ = orc.backproject(orc.depth_to_float(d16), rgb, kt, syn.extrinsic_from_pose(p))
+        clouds.append(P)
+    t0 = time.perf_counter()
+    Nn = orc.estimate_normals(clouds[1], orc.SEARCH_HYBRID, 0.004, 30)
+    t_n = time.perf_counter() - t0
+    ca, sa = np.cos(0.004), np.sin(0.004)
+    T0 = np.array([[ca, -sa, 0, 0.001], [sa, ca, 0, -0.0008], [0, 0, 1, 0.0005], [0, 0, 0, 1.0]])
+    src = clouds[0] @ T0[:3, :3].T + T0[:3, 3]
+    t0 = time.perf_counter()
+    r = orc.registration_icp(src, clouds[1], Nn, max_dist, np.eye(4), 1, 1e-6, 1e-6, 30)
+    dt = time.perf_counter() - t0
+    return {"value": 1.0 / dt, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port", "sample": "1 pair of config 4 "
+            "(2 x %d points, point-to-plane, r = %g m)" % (len(src), max_dist), "iterations": r["iterations"],
+            "estimate_normals_s": t_n}
+
+
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
@@ -273,6 +300,26 @@ def run_gpu(args):
     mirror = ctx.updates_mirror()
     assert mirror == vol.updates(), "host mirror of the step result disagrees with the device counter"
 
+    # ---- the metric's other halves: ICP pairs/s (BASELINE config 4) and mesh extraction of the volume just built ----
+    extra = {}
+    if not args.no_extras:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_extra
+        try:
+            extra["mesh"] = bench_extra.mesh_bench(vol) if world == 1 else None
+        except Exception as e:  # e.g. out of memory for the mesh of a very large volume: report, do not hide
+            extra["mesh"] = {"error": str(e)}
+        vol.reset()
+        icp = bench_extra.icp_bench(args.icp_pairs, 0.004, rank=rank, world=world)
+        if world > 1:
+            t = torch.tensor([icp["ms"]], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            icp["ms"] = float(t.item())
+        icp["pairs"] = args.icp_pairs
+        icp["pairs_per_s"] = args.icp_pairs / (icp["ms"] * 1e-3)
+        icp["distribution"] = "pair p -> GPU p %% %d, no collective" % world
+        extra["icp"] = icp
+
     out = None
     if rank == 0:
         peak, peak_src = peaks()
@@ -305,6 +352,7 @@ def run_gpu(args):
                          "alg_bytes_per_launch": alg_bytes, "bytes_per_update": B_UPD,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
         }
+        out.update(extra)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -319,6 +367,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="tsdf1024", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the ICP pairs/s and mesh-extraction measurements")
+    ap.add_argument("--icp-pairs", type=int, default=64, help="BASELINE config 4: frame pairs of ~300 k points")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -349,6 +399,8 @@ def main():
             fps, ups, n, sample, dt = run_cpu(args.workload, 8, 1, K, budget_s=25.0)
             out["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
                                    "sample": sample, "voxel_updates_per_s": ups}
+            if "icp" in out:
+                out["icp"]["cpu_baseline"] = run_cpu_icp(K)
         print(json.dumps(out))
 
 
