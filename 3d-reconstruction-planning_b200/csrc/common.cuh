@@ -79,7 +79,7 @@ struct b2r_ctx {
     b2r::Scratch small;       // counters, per-frame scalars (zero-initialised on creation)
     b2r::Scratch scan_a, scan_b;
     // marching cubes
-    b2r::Scratch mc_code, mc_flags, mc_block_counts, mc_vert_id;
+    b2r::Scratch mc_code, mc_flags, mc_block_counts, mc_vert_id, mc_live;
     int64_t mc_nv = 0, mc_nt = 0;
     int mc_R = 0, mc_zb = 0, mc_ze = 0;
     // point extraction

@@ -58,6 +58,49 @@ __global__ void __launch_bounds__(PC_THREADS) pc_count_kernel(const float2* __re
     }
 }
 
+// Streaming form of the count pass for even R: a thread loads TWO adjacent voxels with one 16-byte load and only
+// looks at neighbours when one of them is a valid surface candidate (rare); a block of 256 threads covers 512
+// voxels = two count blocks of the emit pass (warps 0-3 / 4-7).
+__global__ void __launch_bounds__(PC_THREADS) pc_count2_kernel(const float2* __restrict__ tsdfw,
+                                                               const __grid_constant__ PcGeom G,
+                                                               uint32_t* __restrict__ blk_counts, int n_count_blocks) {
+    __shared__ uint32_t s_c[PC_THREADS / 32];
+    const int R = G.R;
+    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int64_t t = ((int64_t)blockIdx.x * PC_THREADS + threadIdx.x) * 2;
+    unsigned c = 0;
+    if (t < n) {
+        const int y = (int)(t % R), x = (int)((t / R) % R), z = G.z_begin + (int)(t / ((int64_t)R * R));
+        const float4 q = __ldcs(reinterpret_cast<const float4*>(tsdfw + pidx(R, G.z_begin, x, y, z)));
+        if (pc_valid(make_float2(q.x, q.y))) c += __popc(pc_flags(tsdfw, G, x, y, z));
+        if (pc_valid(make_float2(q.z, q.w))) c += __popc(pc_flags(tsdfw, G, x, y + 1, z));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) s_c[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        const int b = blockIdx.x * 2 + threadIdx.x;
+        if (b < n_count_blocks) {
+            unsigned a = 0;
+            for (int w = 0; w < PC_THREADS / 64; ++w) a += s_c[threadIdx.x * (PC_THREADS / 64) + w];
+            blk_counts[b] = a;
+        }
+    }
+}
+
+// raw per-block counts -> marks -> (scan) -> list of the blocks that produce points: the emit pass is a persistent
+// kernel over that list
+__global__ void __launch_bounds__(256) pc_mark_kernel(const uint32_t* __restrict__ blk_counts, int n, uint32_t* __restrict__ live) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) live[i] = blk_counts[i] != 0u ? 1u : 0u;
+}
+__global__ void __launch_bounds__(256) pc_live_list_kernel(const uint32_t* __restrict__ live, const uint32_t* __restrict__ pos, int n,
+                                                           uint32_t* __restrict__ list) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && live[i]) list[pos[i]] = (uint32_t)i;
+}
+
 // Open3D GetTSDFAt(p): trilinear blend of the 8 surrounding tsdf values (no weight check).
 __device__ __forceinline__ double tsdf_at(const float2* __restrict__ tsdfw, const PcGeom& G, const double* p) {
     int idx[3];
@@ -83,12 +126,17 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
                                                              const uint32_t* __restrict__ color,
                                                              const __grid_constant__ PcGeom G,
                                                              const uint32_t* __restrict__ blk_off,
+                                                             const uint32_t* __restrict__ live_list,
+                                                             const unsigned long long* __restrict__ n_live,
                                                              double* __restrict__ pts, double* __restrict__ nrm,
                                                              double* __restrict__ cols) {
     __shared__ uint32_t smem[33];
     const int R = G.R;
     const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
-    const int64_t t = (int64_t)blockIdx.x * PC_THREADS + threadIdx.x;
+    const unsigned nl = (unsigned)*n_live;
+    for (unsigned li = blockIdx.x; li < nl; li += gridDim.x) {
+    const unsigned vb = live_list[li];
+    const int64_t t = (int64_t)vb * PC_THREADS + threadIdx.x;
     unsigned f = 0;
     int x = 0, y = 0, z = 0;
     if (t < n) {
@@ -97,8 +145,8 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
     }
     uint32_t total;
     const uint32_t local = block_exclusive_scan(__popc(f), smem, &total);
-    if (total == 0 || f == 0) return;
-    int64_t k = (int64_t)blk_off[blockIdx.x] + local;
+    if (total == 0 || f == 0) continue;
+    int64_t k = (int64_t)blk_off[vb] + local;
     const double hvl = 0.5 * G.vl;
     const int64_t i0 = pidx(R, G.z_begin, x, y, z);
     const float f0 = tsdfw[i0].x;
@@ -147,7 +195,9 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
         for (int q = 0; q < 3; ++q) nrm[k * 3 + q] = nn > 0 ? nv[q] / nn : nv[q];
         ++k;
     }
+    }
 }
+
 
 }  // namespace b2r
 
@@ -166,11 +216,22 @@ int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_poi
     if (nz <= 0 || R < 3) return 0;
     const int64_t n = (int64_t)nz * R * R;
     const int nblocks = cdiv(n, PC_THREADS);
-    if (ctx->pc_block_counts.ensure((size_t)nblocks * sizeof(uint32_t))) return -102;
+    if (ctx->pc_block_counts.ensure((size_t)nblocks * 4 * sizeof(uint32_t))) return -102;
     uint32_t* blk = (uint32_t*)ctx->pc_block_counts.ptr;
+    uint32_t* live = blk + nblocks;
+    uint32_t* live_pos = blk + 2 * (size_t)nblocks;
+    uint32_t* live_list = blk + 3 * (size_t)nblocks;
     PcGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
              vol->color_type};
-    pc_count_kernel<<<nblocks, PC_THREADS, 0, st>>>((const float2*)vol->d_tsdfw, G, blk);
+    if (R % 2 == 0 && (((uintptr_t)vol->d_tsdfw) & 15) == 0)
+        pc_count2_kernel<<<cdiv(nblocks, 2), PC_THREADS, 0, st>>>((const float2*)vol->d_tsdfw, G, blk, nblocks);
+    else
+        pc_count_kernel<<<nblocks, PC_THREADS, 0, st>>>((const float2*)vol->d_tsdfw, G, blk);
+    B2R_LAUNCH_CHECK(ctx);
+    pc_mark_kernel<<<cdiv(nblocks, 256), 256, 0, st>>>(blk, nblocks, live);
+    B2R_LAUNCH_CHECK(ctx);
+    if (int rc = scan_exclusive_u32(ctx, live, live_pos, nblocks, (unsigned long long*)ctx->small.ptr + SMALL_PC_NLIVE, st)) return rc;
+    pc_live_list_kernel<<<cdiv(nblocks, 256), 256, 0, st>>>(live, live_pos, nblocks, live_list);
     B2R_LAUNCH_CHECK(ctx);
     unsigned long long* tot = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64_C;
     if (int rc = scan_exclusive_u32(ctx, blk, blk, nblocks, tot, st)) return rc;
@@ -192,8 +253,10 @@ int b2r_extract_points_emit(b2r_ctx* ctx, const b2r_volume* vol, double* d_point
     const int nblocks = cdiv(n, PC_THREADS);
     PcGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
              vol->color_type};
-    pc_emit_kernel<<<nblocks, PC_THREADS, 0, S(stream)>>>((const float2*)vol->d_tsdfw, (const uint32_t*)vol->d_color, G,
-                                                          (const uint32_t*)ctx->pc_block_counts.ptr, d_points,
+    pc_emit_kernel<<<ctx->sm_count * 8, PC_THREADS, 0, S(stream)>>>((const float2*)vol->d_tsdfw, (const uint32_t*)vol->d_color, G,
+                                                          (const uint32_t*)ctx->pc_block_counts.ptr,
+                                                          (const uint32_t*)ctx->pc_block_counts.ptr + 3 * (size_t)nblocks,
+                                                          (const unsigned long long*)ctx->small.ptr + SMALL_PC_NLIVE, d_points,
                                                           d_normals, vol->color_type ? d_colors : nullptr);
     B2R_LAUNCH_CHECK(ctx);
     return 0;

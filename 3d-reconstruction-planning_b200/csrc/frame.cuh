@@ -11,6 +11,8 @@ constexpr int SMALL_NEXT = 9;          // uint32: next work item to hand out
 constexpr int SMALL_TOTAL64 = 128;     // uint64 index (byte 1024): scan totals
 constexpr int SMALL_TOTAL64_B = 129;
 constexpr int SMALL_TOTAL64_C = 130;
+constexpr int SMALL_MC_NLIVE = 131;     // uint64: live virtual blocks of the last b2r_extract_mesh_count
+constexpr int SMALL_PC_NLIVE = 132;     // uint64: live blocks of the last b2r_extract_points_count
 
 constexpr int B2R_MIP_LEVELS = 5;   // max-depth pyramid cells: 8, 16, 32, 64, 128 pixels
 struct MipDesc {

@@ -50,7 +50,8 @@ __device__ __forceinline__ unsigned plane_nibble(const float2* __restrict__ tsdf
 
 // grid: (ceil(R/64), ceil(R/4), nchunks); block (64, 4): threadIdx.x -> y, threadIdx.y -> x
 __global__ void __launch_bounds__(256) mc_classify_kernel(const float2* __restrict__ tsdfw, uint8_t* __restrict__ code,
-                                                          int R, int z_begin, int zc_lo, int zc_hi) {
+                                                          uint8_t* __restrict__ row_active, int R, int z_begin, int zc_lo,
+                                                          int zc_hi) {
     const int y = blockIdx.x * 64 + threadIdx.x;
     const int x = blockIdx.y * 4 + threadIdx.y;
     const int z0 = zc_lo + blockIdx.z * MC_ZCHUNK;
@@ -69,6 +70,7 @@ __global__ void __launch_bounds__(256) mc_classify_kernel(const float2* __restri
         const unsigned c = n_lo | (n_hi << 4);
         const bool active = v_lo && v_hi && c != 0u && c != 255u;
         code[vidx(R, z_begin, x, y, z)] = active ? (uint8_t)c : (uint8_t)0;
+        if (active) row_active[(int64_t)(z - z_begin + B2R_PAD_LO) * R + x] = 1;   // (z, x) row holds an active cube
         n_lo = n_hi; v_lo = v_hi;
     }
 }
@@ -97,39 +99,75 @@ __device__ __forceinline__ unsigned edge_flags(const uint8_t* __restrict__ code,
     return fx | (fy << 1) | (fz << 2);
 }
 
+// Output sensitivity: the surface touches a tiny fraction of the cube, so the per-voxel passes below run only on
+// the "virtual blocks" (256 consecutive voxels = part of one or several (z, x) rows) that can produce anything.
+// A voxel's owned edges / triangles depend on cubes of rows (z, x), (z-1, x), (z, x-1), (z-1, x-1) only; a
+// block none of whose rows has such an active cube is dead: its vert_tab entries stay unwritten (never read) and
+// its totals stay zero.  mc_live marks the live blocks, a scan + compaction turns the marks into a list, and the
+// passes are persistent kernels walking that list (launching a block per 256 voxels of a 1024^3 cube costs more
+// than the work of the live ones).
+__global__ void __launch_bounds__(256) mc_live_kernel(const uint8_t* __restrict__ row_active, int R, int64_t n, int nblocks,
+                                                      uint32_t* __restrict__ live) {
+    const int vb = blockIdx.x * blockDim.x + threadIdx.x;
+    if (vb >= nblocks) return;
+    const int64_t t0 = (int64_t)vb * MC_THREADS;
+    const int64_t t1 = min(t0 + MC_THREADS, n) - 1;
+    unsigned any = 0;
+    for (int64_t r = t0 / R; r <= t1 / R; ++r) {
+        const int64_t zr = r / R;
+        const int x = (int)(r - zr * R);
+        const int64_t a = (zr + B2R_PAD_LO) * R + x;     // padded plane index >= 1: the plane below always exists
+        any |= row_active[a] | row_active[a - R];
+        if (x > 0) any |= row_active[a - 1] | row_active[a - R - 1];
+    }
+    live[vb] = any ? 1u : 0u;
+}
+__global__ void __launch_bounds__(256) mc_live_list_kernel(const uint32_t* __restrict__ live, const uint32_t* __restrict__ pos,
+                                                           int nblocks, uint32_t* __restrict__ list) {
+    const int vb = blockIdx.x * blockDim.x + threadIdx.x;
+    if (vb < nblocks && live[vb]) list[pos[vb]] = (uint32_t)vb;
+}
+
 // flat thread per owned voxel (memory order).  Writes vert_tab[voxel] = flags << 29 (ids are added by
 // mc_emit_vertices) and per-block totals.
 __global__ void __launch_bounds__(MC_THREADS) mc_count_kernel(const uint8_t* __restrict__ code, int R, int z_begin,
                                                               int z_end, int zc_lo, int zc_hi,
+                                                              const uint32_t* __restrict__ live_list,
+                                                              const unsigned long long* __restrict__ n_live,
                                                               uint32_t* __restrict__ vert_tab,
                                                               uint32_t* __restrict__ blk_verts,
                                                               uint32_t* __restrict__ blk_tris) {
     __shared__ uint32_t s_v[MC_THREADS / 32], s_t[MC_THREADS / 32];
     const int64_t n = (int64_t)(z_end - z_begin) * R * R;
-    const int64_t t = (int64_t)blockIdx.x * MC_THREADS + threadIdx.x;
-    unsigned nv = 0, nt = 0;
-    if (t < n) {
-        const int y = (int)(t % R), x = (int)((t / R) % R), z = z_begin + (int)(t / ((int64_t)R * R));
-        unsigned own;
-        const unsigned f = edge_flags(code, R, z_begin, zc_lo, zc_hi, x, y, z, own);
-        nv = __popc(f);
-        nt = d_mc_ntri_table[own];
-        vert_tab[vidx(R, z_begin, x, y, z)] = f << 29;
-    }
-    // warp shuffle reduction, then one shared-memory pass per block
+    const unsigned nl = (unsigned)*n_live;
+    for (unsigned li = blockIdx.x; li < nl; li += gridDim.x) {
+        const unsigned vb = live_list[li];
+        const int64_t t = (int64_t)vb * MC_THREADS + threadIdx.x;
+        unsigned nv = 0, nt = 0;
+        if (t < n) {
+            const int y = (int)(t % R), x = (int)((t / R) % R), z = z_begin + (int)(t / ((int64_t)R * R));
+            unsigned own;
+            const unsigned f = edge_flags(code, R, z_begin, zc_lo, zc_hi, x, y, z, own);
+            nv = __popc(f);
+            nt = d_mc_ntri_table[own];
+            vert_tab[vidx(R, z_begin, x, y, z)] = f << 29;
+        }
+        // warp shuffle reduction, then one shared-memory pass per block
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        nv += __shfl_xor_sync(0xffffffffu, nv, o);
-        nt += __shfl_xor_sync(0xffffffffu, nt, o);
-    }
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane == 0) { s_v[warp] = nv; s_t[warp] = nt; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned a = 0, b = 0;
-        for (int w = 0; w < MC_THREADS / 32; ++w) { a += s_v[w]; b += s_t[w]; }
-        blk_verts[blockIdx.x] = a;
-        blk_tris[blockIdx.x] = b;
+        for (int o = 16; o > 0; o >>= 1) {
+            nv += __shfl_xor_sync(0xffffffffu, nv, o);
+            nt += __shfl_xor_sync(0xffffffffu, nt, o);
+        }
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (lane == 0) { s_v[warp] = nv; s_t[warp] = nt; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned a = 0, b = 0;
+            for (int w = 0; w < MC_THREADS / 32; ++w) { a += s_v[w]; b += s_t[w]; }
+            blk_verts[vb] = a;
+            blk_tris[vb] = b;
+        }
+        __syncthreads();
     }
 }
 
@@ -147,6 +185,8 @@ __device__ __forceinline__ void decode_color(uint32_t c, int color_type, double*
 __global__ void __launch_bounds__(MC_THREADS) mc_emit_vertices_kernel(const float2* __restrict__ tsdfw,
                                                                       const uint32_t* __restrict__ color,
                                                                       const __grid_constant__ McGeom G,
+                                                                      const uint32_t* __restrict__ live_list,
+                                                                      const unsigned long long* __restrict__ n_live,
                                                                       uint32_t* __restrict__ vert_tab,
                                                                       const uint32_t* __restrict__ blk_off,
                                                                       uint32_t vertex_base, double* __restrict__ verts,
@@ -154,82 +194,92 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_vertices_kernel(const floa
     __shared__ uint32_t smem[33];
     const int R = G.R;
     const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
-    const int64_t t = (int64_t)blockIdx.x * MC_THREADS + threadIdx.x;
-    unsigned f = 0;
-    int x = 0, y = 0, z = 0;
-    int64_t vi = 0;
-    if (t < n) {
-        y = (int)(t % R); x = (int)((t / R) % R); z = G.z_begin + (int)(t / ((int64_t)R * R));
-        vi = vidx(R, G.z_begin, x, y, z);
-        f = vert_tab[vi] >> 29;
-    }
-    uint32_t total;
-    const uint32_t local = block_exclusive_scan(__popc(f), smem, &total);
-    if (total == 0 || f == 0) return;
-    const uint32_t first_local = blk_off[blockIdx.x] + local;  // id within this slab
-    vert_tab[vi] = (f << 29) | (vertex_base + first_local);
-    const double hvl = 0.5 * G.vl;
-    const float f0s = tsdfw[vi].x;
-    double c0[3] = {0, 0, 0};
-    if (vcols && G.color_type) decode_color(color[vi], G.color_type, c0);
-    uint32_t k = first_local;
-#pragma unroll
-    for (int a = 0; a < 3; ++a) {
-        if (!(f & (1u << a))) continue;
-        const int64_t ni = vi + (a == 0 ? (int64_t)R : a == 1 ? (int64_t)1 : (int64_t)R * R);
-        const float f1s = tsdfw[ni].x;
-        const double f0 = fabs((double)f0s), f1 = fabs((double)f1s);
-        double pt[3] = {hvl + G.vl * (double)x, hvl + G.vl * (double)y, hvl + G.vl * (double)z};
-        pt[a] += f0 * G.vl / (f0 + f1);
-        verts[(int64_t)k * 3 + 0] = pt[0] + G.ox;
-        verts[(int64_t)k * 3 + 1] = pt[1] + G.oy;
-        verts[(int64_t)k * 3 + 2] = pt[2] + G.oz;
-        if (vcols && G.color_type) {
-            double c1[3];
-            decode_color(color[ni], G.color_type, c1);
-#pragma unroll
-            for (int q = 0; q < 3; ++q) vcols[(int64_t)k * 3 + q] = (f1 * c0[q] + f0 * c1[q]) / (f0 + f1);
+    const unsigned nl = (unsigned)*n_live;
+    for (unsigned li = blockIdx.x; li < nl; li += gridDim.x) {
+        const unsigned vb = live_list[li];
+        const int64_t t = (int64_t)vb * MC_THREADS + threadIdx.x;
+        unsigned f = 0;
+        int x = 0, y = 0, z = 0;
+        int64_t vi = 0;
+        if (t < n) {
+            y = (int)(t % R); x = (int)((t / R) % R); z = G.z_begin + (int)(t / ((int64_t)R * R));
+            vi = vidx(R, G.z_begin, x, y, z);
+            f = vert_tab[vi] >> 29;
         }
-        ++k;
+        uint32_t total;
+        const uint32_t local = block_exclusive_scan(__popc(f), smem, &total);
+        if (total == 0 || f == 0) continue;
+        const uint32_t first_local = blk_off[vb] + local;  // id within this slab
+        vert_tab[vi] = (f << 29) | (vertex_base + first_local);
+        const double hvl = 0.5 * G.vl;
+        const float f0s = tsdfw[vi].x;
+        double c0[3] = {0, 0, 0};
+        if (vcols && G.color_type) decode_color(color[vi], G.color_type, c0);
+        uint32_t k = first_local;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            if (!(f & (1u << a))) continue;
+            const int64_t ni = vi + (a == 0 ? (int64_t)R : a == 1 ? (int64_t)1 : (int64_t)R * R);
+            const float f1s = tsdfw[ni].x;
+            const double f0 = fabs((double)f0s), f1 = fabs((double)f1s);
+            double pt[3] = {hvl + G.vl * (double)x, hvl + G.vl * (double)y, hvl + G.vl * (double)z};
+            pt[a] += f0 * G.vl / (f0 + f1);
+            verts[(int64_t)k * 3 + 0] = pt[0] + G.ox;
+            verts[(int64_t)k * 3 + 1] = pt[1] + G.oy;
+            verts[(int64_t)k * 3 + 2] = pt[2] + G.oz;
+            if (vcols && G.color_type) {
+                double c1[3];
+                decode_color(color[ni], G.color_type, c1);
+#pragma unroll
+                for (int q = 0; q < 3; ++q) vcols[(int64_t)k * 3 + q] = (f1 * c0[q] + f0 * c1[q]) / (f0 + f1);
+            }
+            ++k;
+        }
     }
 }
 
 __global__ void __launch_bounds__(MC_THREADS) mc_emit_triangles_kernel(const uint8_t* __restrict__ code,
                                                                        const uint32_t* __restrict__ vert_tab, int R,
                                                                        int z_begin, int z_end, int zc_hi,
+                                                                       const uint32_t* __restrict__ live_list,
+                                                                       const unsigned long long* __restrict__ n_live,
                                                                        const uint32_t* __restrict__ blk_off,
                                                                        int32_t* __restrict__ tris) {
     __shared__ uint32_t smem[33];
     const int64_t n = (int64_t)(z_end - z_begin) * R * R;
-    const int64_t t = (int64_t)blockIdx.x * MC_THREADS + threadIdx.x;
-    unsigned c = 0;
-    int x = 0, y = 0, z = 0;
-    if (t < n) {
-        y = (int)(t % R); x = (int)((t / R) % R); z = z_begin + (int)(t / ((int64_t)R * R));
-        if (z <= zc_hi) c = code[vidx(R, z_begin, x, y, z)];
-    }
-    const unsigned nt = d_mc_ntri_table[c];
-    uint32_t total;
-    const uint32_t local = block_exclusive_scan(nt, smem, &total);
-    if (total == 0 || nt == 0) return;
-    int64_t o = ((int64_t)blk_off[blockIdx.x] + local) * 3;
-    int ids[12];
-#pragma unroll
-    for (int e = 0; e < 12; ++e) {
-        ids[e] = -1;
-        if (d_mc_edge_table[c] & (1 << e)) {
-            const int ex = x + d_mc_edge_shift[e][0], ey = y + d_mc_edge_shift[e][1], ez = z + d_mc_edge_shift[e][2];
-            const int axis = d_mc_edge_shift[e][3];
-            const uint32_t ent = __ldg(&vert_tab[vidx(R, z_begin, ex, ey, ez)]);
-            const unsigned fl = ent >> 29;
-            ids[e] = (int)((ent & 0x1fffffffu) + __popc(fl & ((1u << axis) - 1u)));
+    const unsigned nl = (unsigned)*n_live;
+    for (unsigned li = blockIdx.x; li < nl; li += gridDim.x) {
+        const unsigned vb = live_list[li];
+        const int64_t t = (int64_t)vb * MC_THREADS + threadIdx.x;
+        unsigned c = 0;
+        int x = 0, y = 0, z = 0;
+        if (t < n) {
+            y = (int)(t % R); x = (int)((t / R) % R); z = z_begin + (int)(t / ((int64_t)R * R));
+            if (z <= zc_hi) c = code[vidx(R, z_begin, x, y, z)];
         }
-    }
-    for (int i = 0; i < 15 && d_mc_tri_table[c][i] != -1; i += 3) {
-        tris[o + 0] = ids[d_mc_tri_table[c][i]];
-        tris[o + 1] = ids[d_mc_tri_table[c][i + 2]];
-        tris[o + 2] = ids[d_mc_tri_table[c][i + 1]];
-        o += 3;
+        const unsigned nt = d_mc_ntri_table[c];
+        uint32_t total;
+        const uint32_t local = block_exclusive_scan(nt, smem, &total);
+        if (total == 0 || nt == 0) continue;
+        int64_t o = ((int64_t)blk_off[vb] + local) * 3;
+        int ids[12];
+#pragma unroll
+        for (int e = 0; e < 12; ++e) {
+            ids[e] = -1;
+            if (d_mc_edge_table[c] & (1 << e)) {
+                const int ex = x + d_mc_edge_shift[e][0], ey = y + d_mc_edge_shift[e][1], ez = z + d_mc_edge_shift[e][2];
+                const int axis = d_mc_edge_shift[e][3];
+                const uint32_t ent = __ldg(&vert_tab[vidx(R, z_begin, ex, ey, ez)]);
+                const unsigned fl = ent >> 29;
+                ids[e] = (int)((ent & 0x1fffffffu) + __popc(fl & ((1u << axis) - 1u)));
+            }
+        }
+        for (int i = 0; i < 15 && d_mc_tri_table[c][i] != -1; i += 3) {
+            tris[o + 0] = ids[d_mc_tri_table[c][i]];
+            tris[o + 1] = ids[d_mc_tri_table[c][i + 2]];
+            tris[o + 2] = ids[d_mc_tri_table[c][i + 1]];
+            o += 3;
+        }
     }
 }
 
@@ -269,15 +319,30 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
     uint32_t* blk_t = blk_v + nblocks;
     int zc_lo, zc_hi;
     cube_z_range(vol, zc_lo, zc_hi);
+    if (ctx->mc_flags.ensure(planes * R)) return -102;
+    uint8_t* row_active = (uint8_t*)ctx->mc_flags.ptr;
+    B2R_CUDA(cudaMemsetAsync(row_active, 0, planes * R, st));
     B2R_CUDA(cudaMemsetAsync(code, 0, nvox_pad, st));
     if (zc_hi >= zc_lo) {
         dim3 block(64, 4), grid(cdiv(R, 64), cdiv(R, 4), cdiv(zc_hi - zc_lo + 1, MC_ZCHUNK));
-        mc_classify_kernel<<<grid, block, 0, st>>>((const float2*)vol->d_tsdfw, code, R, zb, zc_lo, zc_hi);
+        mc_classify_kernel<<<grid, block, 0, st>>>((const float2*)vol->d_tsdfw, code, row_active, R, zb, zc_lo, zc_hi);
         B2R_LAUNCH_CHECK(ctx);
     }
-    mc_count_kernel<<<nblocks, MC_THREADS, 0, st>>>(code, R, zb, ze, zc_lo, zc_hi, vert_tab, blk_v, blk_t);
-    B2R_LAUNCH_CHECK(ctx);
     unsigned long long* tot = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64;
+    // live virtual blocks -> list (device-side count in tot[2]); dead blocks keep zero totals
+    if (ctx->mc_live.ensure((size_t)nblocks * 3 * sizeof(uint32_t))) return -102;
+    uint32_t* live = (uint32_t*)ctx->mc_live.ptr;
+    uint32_t* live_pos = live + nblocks;
+    uint32_t* live_list = live + 2 * (size_t)nblocks;
+    mc_live_kernel<<<cdiv(nblocks, 256), 256, 0, st>>>(row_active, R, n, nblocks, live);
+    B2R_LAUNCH_CHECK(ctx);
+    if (int rc = scan_exclusive_u32(ctx, live, live_pos, nblocks, (unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE, st)) return rc;
+    mc_live_list_kernel<<<cdiv(nblocks, 256), 256, 0, st>>>(live, live_pos, nblocks, live_list);
+    B2R_LAUNCH_CHECK(ctx);
+    B2R_CUDA(cudaMemsetAsync(blk_v, 0, (size_t)nblocks * 2 * sizeof(uint32_t), st));
+    mc_count_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, st>>>(code, R, zb, ze, zc_lo, zc_hi, live_list, (unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE, vert_tab, blk_v,
+                                                              blk_t);
+    B2R_LAUNCH_CHECK(ctx);
     if (int rc = scan_exclusive_u32(ctx, blk_v, blk_v, nblocks, tot, st)) return rc;
     if (int rc = scan_exclusive_u32(ctx, blk_t, blk_t, nblocks, tot + 1, st)) return rc;
     B2R_CUDA(cudaMemcpyAsync(ctx->pinned, tot, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
@@ -310,8 +375,11 @@ int b2r_extract_mesh_vertices(b2r_ctx* ctx, const b2r_volume* vol, int64_t verte
     const int nblocks = cdiv(n, MC_THREADS);
     McGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
              vol->color_type};
-    mc_emit_vertices_kernel<<<nblocks, MC_THREADS, 0, S(stream)>>>(
-        (const float2*)vol->d_tsdfw, (const uint32_t*)vol->d_color, G, (uint32_t*)ctx->mc_vert_id.ptr,
+    const uint32_t* live_list = (const uint32_t*)ctx->mc_live.ptr + 2 * (size_t)nblocks;
+    const unsigned long long* n_live = (const unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE;
+    mc_emit_vertices_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, S(stream)>>>(
+        (const float2*)vol->d_tsdfw, (const uint32_t*)vol->d_color, G, live_list, n_live,
+        (uint32_t*)ctx->mc_vert_id.ptr,
         (const uint32_t*)ctx->mc_block_counts.ptr, (uint32_t)vertex_base, d_vertices,
         vol->color_type ? d_colors : nullptr);
     B2R_LAUNCH_CHECK(ctx);
@@ -340,9 +408,12 @@ int b2r_extract_mesh_triangles(b2r_ctx* ctx, const b2r_volume* vol, int32_t* d_t
     int zc_lo, zc_hi;
     cube_z_range(vol, zc_lo, zc_hi);
     const uint32_t* blk_t = (const uint32_t*)ctx->mc_block_counts.ptr + nblocks;
-    mc_emit_triangles_kernel<<<nblocks, MC_THREADS, 0, S(stream)>>>((const uint8_t*)ctx->mc_code.ptr,
-                                                                    (const uint32_t*)ctx->mc_vert_id.ptr, R,
-                                                                    vol->z_begin, vol->z_end, zc_hi, blk_t, d_triangles);
+    const uint32_t* live_list = (const uint32_t*)ctx->mc_live.ptr + 2 * (size_t)nblocks;
+    const unsigned long long* n_live = (const unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE;
+    mc_emit_triangles_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, S(stream)>>>((const uint8_t*)ctx->mc_code.ptr,
+                                                                              (const uint32_t*)ctx->mc_vert_id.ptr, R,
+                                                                              vol->z_begin, vol->z_end, zc_hi, live_list, n_live,
+                                                                              blk_t, d_triangles);
     B2R_LAUNCH_CHECK(ctx);
     return 0;
 }

@@ -36,7 +36,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s
 }
 
 // out[i] = sum_{j<i} in[j]; *d_total (uint64, optional) = sum of all.  in may alias out.
-// Single persistent block; 8 items per thread per tile, 128-bit loads when aligned.
+// Tiled: per-tile sums, scan of the tile sums, per-tile scan (three launches; scratch in ctx->scan_b).
 int scan_exclusive_u32(b2r_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, int64_t n,
                        unsigned long long* d_total, cudaStream_t stream);
 
