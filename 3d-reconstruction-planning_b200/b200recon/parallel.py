@@ -43,6 +43,45 @@ def slab_ranges(resolution, world):
     return [slab_range(resolution, r, world) for r in range(world)]
 
 
+def balanced_slab_ranges(plane_work, world, min_planes=4):
+    """Contiguous z-slabs with (nearly) equal WORK instead of equal plane counts.  Integration only touches the
+    voxels between the cameras and the surfaces, which on a table-top orbit is the lower part of the cube: equal
+    slabs leave most ranks idle.  `plane_work[z]` = expected voxel updates per frame sequence in plane z (see
+    `probe_plane_work`); returns [(z_begin, z_end)] per rank, every slab at least `min_planes` thick (halo)."""
+    w = np.asarray(plane_work, np.float64).reshape(-1)
+    R = len(w)
+    if world * min_planes > R:
+        raise RuntimeError("%d planes cannot give %d slabs of >= %d planes" % (R, world, min_planes))
+    w = np.maximum(w, 0.0)
+    w = w + (w.sum() * 1e-3 / R + 1e-30)      # a small per-plane cost: empty regions are still split, not piled on one rank
+    c = np.concatenate([[0.0], np.cumsum(w)])
+    cuts = [0]
+    for k in range(1, world):
+        z = int(np.searchsorted(c, c[-1] * k / world))
+        z = max(z, cuts[-1] + min_planes)
+        z = min(z, R - (world - k) * min_planes)
+        cuts.append(z)
+    cuts.append(R)
+    return [(cuts[i], cuts[i + 1]) for i in range(world)]
+
+
+def probe_plane_work(length, resolution, sdf_trunc, origin, frames, intrinsic, probe_resolution=128, device=None):
+    """Per-plane work estimate for `balanced_slab_ranges`: integrates `frames` -- an iterable of (depth_f32 CUDA
+    tensor [H,W] in metres, extrinsic 4x4) -- into a coarse NoColor copy of the cube (probe_resolution^3, same
+    length/origin) and counts the updates per z plane (weight = number of frames that updated a voxel).  Every
+    rank runs the same probe on the same frames and gets the same answer: no collective."""
+    from .pipelines import integration
+    Rp = int(min(probe_resolution, resolution))
+    vol = integration.UniformTSDFVolume(length, Rp, max(sdf_trunc, length / Rp), integration.TSDFVolumeColorType.NoColor,
+                                        origin, device=device)
+    for depth_f32, ext in frames:
+        vol.integrate_device(depth_f32, None, intrinsic, ext)
+    _, w, _ = vol.export_arrays()                    # [x, y, z]
+    per_plane = np.asarray(w, np.float64).sum(axis=(0, 1))
+    rep = int(np.ceil(resolution / Rp))
+    return np.repeat(per_plane, rep)[: int(resolution)] / rep
+
+
 # --------------------------------------------------------------------------------------------------
 # halo exchange
 # --------------------------------------------------------------------------------------------------
@@ -156,13 +195,22 @@ class SlabVolume:
 
     The mesh is the single-volume mesh: same vertex and triangle sets (vertex ids are global)."""
 
-    def __init__(self, length, resolution, sdf_trunc, color_type=None, origin=(0.0, 0.0, 0.0), group=None, device=None):
+    def __init__(self, length, resolution, sdf_trunc, color_type=None, origin=(0.0, 0.0, 0.0), group=None, device=None,
+                 z_ranges=None):
+        """z_ranges: optional [(z_begin, z_end)] per rank (contiguous, covering [0, resolution)), e.g. from
+        `balanced_slab_ranges`; default = equal plane counts."""
         from .pipelines import integration
         self.group = group
         self.rank, self.world = world_info(group)
         self.resolution = int(resolution)
         ct = integration.TSDFVolumeColorType.RGB8 if color_type is None else color_type
-        self.z_begin, self.z_end = slab_range(resolution, self.rank, self.world)
+        if z_ranges is None:
+            z_ranges = slab_ranges(resolution, self.world)
+        z_ranges = [(int(a), int(b)) for a, b in z_ranges]
+        if (len(z_ranges) != self.world or z_ranges[0][0] != 0 or z_ranges[-1][1] != self.resolution or
+                any(z_ranges[i][1] != z_ranges[i + 1][0] for i in range(self.world - 1))):
+            raise RuntimeError("SlabVolume: z_ranges must be %d contiguous slabs covering [0, %d)" % (self.world, self.resolution))
+        self.z_begin, self.z_end = z_ranges[self.rank]
         if self.world > 1 and (self.z_end - self.z_begin) < max(_lib.PAD_LO, _lib.PAD_HI):
             raise RuntimeError("SlabVolume: %d planes over %d ranks leaves slabs thinner than the halo" %
                                (self.resolution, self.world))

@@ -210,12 +210,6 @@ def run_gpu(args):
     ctx = runtime.ctx(local)
     dev = ctx.tdev
 
-    # z-slab owned by this rank
-    zb, ze = R * rank // world, R * (rank + 1) // world
-    vol = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
-                                                      syn.volume_origin(L), z_range=(zb, ze), device=local)
-    vol.count_updates = False   # switched on for the counting pass and the e2e pass only
-
     # synthetic frames: ray-cast on this GPU (resident in HBM), raw uint16 depth + uint8 colour
     nf = min(len(poses), max(args.steps + args.warmup, 1))
     d16 = torch.empty((nf, K["height"], K["width"]), dtype=torch.uint16, device=dev)
@@ -231,6 +225,21 @@ def run_gpu(args):
     for i in range(nf):
         _lib.check(_lib.load().b2r_depth_to_float(ctx.handle, runtime.ptr(d16[i]), 1, K["height"], K["width"], 1000.0,
                                                   3.0, runtime.ptr(depth_f[i]), ctx.stream()))
+    # z-slab owned by this rank.  Equal plane counts would leave most ranks idle (a table-top orbit only touches the
+    # planes between the cameras and the table), so the slab boundaries come from a coarse probe integration of 16
+    # frames of the sequence: contiguous slabs of equal WORK (parallel.balanced_slab_ranges); every rank computes the
+    # same boundaries, no collective.
+    from b200recon import parallel
+    if world > 1 and not args.equal_slabs:
+        probe = [(depth_f[k], exts[k]) for k in range(0, nf, max(1, nf // 16))]
+        work = parallel.probe_plane_work(L, R, trunc, syn.volume_origin(L), probe, intr, probe_resolution=128, device=local)
+        ranges = parallel.balanced_slab_ranges(work, world)
+    else:
+        ranges = parallel.slab_ranges(R, world)
+    zb, ze = ranges[rank]
+    vol = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
+                                                      syn.volume_origin(L), z_range=(zb, ze), device=local)
+    vol.count_updates = False   # switched on for the counting pass and the e2e pass only
     # pinned host copies for the e2e arm
     d16_h = d16.cpu().pin_memory()
     rgb_h = rgb.cpu().pin_memory()
@@ -271,6 +280,7 @@ def run_gpu(args):
         ms = e0.elapsed_time(e1)
         clocks = sampler.stop() if sampler else None
         upd = vol.updates() - upd0
+        timed.local_updates = upd          # this rank's own share (roofline of rank 0's kernel)
         launches = ctx.launch_count() - l0
         if world > 1:
             t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -295,7 +305,7 @@ def run_gpu(args):
     # count is a deterministic function of the frame sequence since reset)
     vol.count_updates = True
     _, upd, _, _ = timed(step_dev, args.steps, args.warmup)
-    upd_k = upd
+    upd_k_local = timed.local_updates
     e_ms, e_upd, _, _ = timed(step_e2e, args.steps, args.warmup)
     mirror = ctx.updates_mirror()
     assert mirror == vol.updates(), "host mirror of the step result disagrees with the device counter"
@@ -324,7 +334,7 @@ def run_gpu(args):
     if rank == 0:
         peak, peak_src = peaks()
         nz_frac = (ze - zb) / R
-        upd_rank0_per_launch = (upd_k / world) / max(args.steps, 1)  # slabs see ~equal shares over an orbit
+        upd_rank0_per_launch = upd_k_local / max(args.steps, 1)      # rank 0's own slab, its own kernel time
         alg_bytes = upd_rank0_per_launch * B_UPD + frame_bytes(K)
         achieved = alg_bytes / (k_ms_timed / max(args.steps, 1) * 1e-3) / 1e9
         fps = args.steps / (ms * 1e-3)
@@ -334,7 +344,7 @@ def run_gpu(args):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "resolution": R, "voxel_mm": 1000.0 * L / R, "frames_in_orbit": len(poses),
-                       "frame": "640x480 uint16 depth + uint8 rgb", "sharding": "z-slab x%d" % world,
+                       "frame": "640x480 uint16 depth + uint8 rgb", "sharding": "z-slab x%d" % world, "slab_boundaries": [a for a, _ in ranges] + [R],
                        "l2": "volume (%.1f GB) >> L2; consecutive frames touch overlapping voxels as in a real "
                              "sequence, no artificial flush" % (R ** 3 * 12 / 1e9)},
             "voxel_updates_per_s": upd / (ms * 1e-3),
@@ -367,6 +377,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="tsdf1024", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--equal-slabs", action="store_true", help="N > 1: equal plane counts instead of work-balanced slabs")
     ap.add_argument("--no-extras", action="store_true", help="skip the ICP pairs/s and mesh-extraction measurements")
     ap.add_argument("--icp-pairs", type=int, default=64, help="BASELINE config 4: frame pairs of ~300 k points")
     args = ap.parse_args()

@@ -50,7 +50,16 @@ def main():
     frames = hp.make_frames(5, K)
     origin = syn.volume_origin(L)
     intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], *hp.kt(K))
-    vol = parallel.SlabVolume(L, R, trunc, RGB8, origin)
+    # work-balanced (unequal) slabs from a coarse probe integration of the same frames -- what bench.py shards with
+    from b200recon import runtime
+    probe = []
+    for d16, rgb, ext in frames:
+        df = torch.from_numpy(orc.depth_to_float(d16)).to(runtime.ctx().tdev)
+        probe.append((df, ext))
+    work = parallel.probe_plane_work(L, R, trunc, origin, probe, intr, probe_resolution=32)
+    ranges = parallel.balanced_slab_ranges(work, world)
+    assert ranges[0][0] == 0 and ranges[-1][1] == R
+    vol = parallel.SlabVolume(L, R, trunc, RGB8, origin, z_ranges=ranges)
     ref = orc.UniformTSDFVolume(L, R, trunc, 1, origin)
     for d16, rgb, ext in frames:
         vol.integrate_host(d16, rgb, intr, ext)

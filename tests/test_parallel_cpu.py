@@ -108,3 +108,27 @@ def test_halo_plan_messages_pair_up():
 def test_world_info_without_process_group():
     assert parallel.world_info() == (0, 1)
     assert np.array_equal(parallel.exclusive_bases([3, 0, 5]), [0, 3, 3])
+
+
+def test_balanced_slab_ranges():
+    from b200recon import parallel
+    R = 1024
+    w = np.zeros(R)
+    w[100:330] = np.linspace(3.0, 1.0, 230)          # all the work in the lower third (table-top orbit)
+    for world in (1, 2, 3, 4, 8):
+        rg = parallel.balanced_slab_ranges(w, world)
+        assert len(rg) == world and rg[0][0] == 0 and rg[-1][1] == R
+        assert all(rg[i][1] == rg[i + 1][0] for i in range(world - 1))
+        assert all(b - a >= 4 for a, b in rg)
+        share = np.array([w[a:b].sum() for a, b in rg]) / w.sum()
+        assert share.max() <= 1.0 / world + 0.02, (world, share)
+    # no work at all: still a valid partition, roughly equal
+    rg = parallel.balanced_slab_ranges(np.zeros(64), 4)
+    assert [b - a for a, b in rg] == [16, 16, 16, 16]
+    # minimum thickness wins over balance when the work sits in very few planes
+    w2 = np.zeros(64)
+    w2[10] = 1.0
+    rg = parallel.balanced_slab_ranges(w2, 8)
+    assert all(b - a >= 4 for a, b in rg) and rg[-1][1] == 64
+    with pytest.raises(RuntimeError):
+        parallel.balanced_slab_ranges(np.ones(16), 8)
