@@ -237,6 +237,12 @@ def run_gpu(args):
     else:
         ranges = parallel.slab_ranges(R, world)
     zb, ze = ranges[rank]
+    if args.emulate_rank:      # tuning aid: one rank's slab of an N-way split on a single GPU (not a bench line)
+        r_, n_ = [int(v) for v in args.emulate_rank.split("/")]
+        probe = [(depth_f[k], exts[k]) for k in range(0, nf, max(1, nf // 16))]
+        work = parallel.probe_plane_work(L, R, trunc, syn.volume_origin(L), probe, intr, probe_resolution=128, device=local)
+        ranges = parallel.balanced_slab_ranges(work, n_)
+        zb, ze = ranges[r_]
     vol = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
                                                       syn.volume_origin(L), z_range=(zb, ze), device=local)
     vol.count_updates = False   # switched on for the counting pass and the e2e pass only
@@ -369,7 +375,20 @@ def run_gpu(args):
     return out
 
 
+def emit(obj):
+    """The one JSON line of the contract, written to the ORIGINAL stdout (libraries -- NCCL's version banner, torchrun
+    -- print to fd 1 too; everything else of this process is sent to stderr, see main)."""
+    os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)           # fd 1 -> stderr for everything except emit()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=256)
@@ -378,6 +397,7 @@ def main():
     ap.add_argument("--workload", default="tsdf1024", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--equal-slabs", action="store_true", help="N > 1: equal plane counts instead of work-balanced slabs")
+    ap.add_argument("--emulate-rank", default="", help="r/N: run rank r's slab of an N-way split on one GPU (tuning aid)")
     ap.add_argument("--no-extras", action="store_true", help="skip the ICP pairs/s and mesh-extraction measurements")
     ap.add_argument("--icp-pairs", type=int, default=64, help="BASELINE config 4: frame pairs of ~300 k points")
     args = ap.parse_args()
@@ -392,7 +412,7 @@ def main():
         fps, ups, n, sample, dt = run_cpu(args.workload, args.steps, args.warmup, K, budget_s=120.0)
         cores = os.cpu_count()
         R = WORKLOADS[args.workload][0]
-        print(json.dumps({
+        emit(({
             "impl": "reference", "metric": "TSDF integration frames/s (640x480 RGB-D into dense TSDF+colour volume)",
             "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": n, "warmup": args.warmup,
             "ms_per_step": 1000.0 / fps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -412,7 +432,7 @@ def main():
                                    "sample": sample, "voxel_updates_per_s": ups}
             if "icp" in out:
                 out["icp"]["cpu_baseline"] = run_cpu_icp(K)
-        print(json.dumps(out))
+        emit(out)
 
 
 if __name__ == "__main__":
