@@ -65,6 +65,19 @@ def balanced_slab_ranges(plane_work, world, min_planes=4):
     return [(cuts[i], cuts[i + 1]) for i in range(world)]
 
 
+def rebalance_slab_ranges(ranges, plane_work, times, min_planes=4):
+    """One feedback step on top of `balanced_slab_ranges`: `times[r]` = measured integration time of rank r on
+    its slab `ranges[r]` (any unit).  Updates are not the whole cost -- slabs under the surfaces still sample voxels
+    they then reject, slabs near a camera have half-empty tiles -- so the per-plane work estimate of every slab is
+    rescaled to the time that slab really took, and the cube is cut again into slabs of equal estimated time."""
+    w = np.maximum(np.asarray(plane_work, np.float64).reshape(-1), 0.0)
+    w = w + (w.sum() * 1e-3 / len(w) + 1e-30)
+    cost = np.zeros_like(w)
+    for (a, b), t in zip(ranges, times):
+        cost[a:b] = w[a:b] * (float(t) / w[a:b].sum())
+    return balanced_slab_ranges(cost, len(ranges), min_planes)
+
+
 def probe_plane_work(length, resolution, sdf_trunc, origin, frames, intrinsic, probe_resolution=128, device=None):
     """Per-plane work estimate for `balanced_slab_ranges`: integrates `frames` -- an iterable of (depth_f32 CUDA
     tensor [H,W] in metres, extrinsic 4x4) -- into a coarse NoColor copy of the cube (probe_resolution^3, same

@@ -234,6 +234,26 @@ def run_gpu(args):
         probe = [(depth_f[k], exts[k]) for k in range(0, nf, max(1, nf // 16))]
         work = parallel.probe_plane_work(L, R, trunc, syn.volume_origin(L), probe, intr, probe_resolution=128, device=local)
         ranges = parallel.balanced_slab_ranges(work, world)
+        # two feedback steps: time the streaming kernel of every rank on its slab over 12 frames, rescale the work
+        # estimate of each slab to its measured time, cut again (setup, outside the timed region; one all_gather of a float)
+        for _ in range(2):
+            zb, ze = ranges[rank]
+            v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
+                                                            syn.volume_origin(L), z_range=(zb, ze), device=local)
+            v.count_updates = False
+            for k in range(3):
+                v.integrate_device(depth_f[k % nf], rgb[k % nf], intr, exts[k % nf])
+            ctx.kernel_timing(True)
+            for k in range(0, nf, max(1, nf // 12)):
+                v.integrate_device(depth_f[k], rgb[k], intr, exts[k])
+            ctx.kernel_timing(False)
+            t_ms, t_n = ctx.kernel_time()
+            tt = torch.zeros(world, dtype=torch.float64, device=dev)
+            tt[rank] = t_ms / max(t_n, 1)
+            dist.all_reduce(tt)
+            ranges = parallel.rebalance_slab_ranges(ranges, work, tt.cpu().numpy())
+            del v
+            torch.cuda.empty_cache()
     else:
         ranges = parallel.slab_ranges(R, world)
     zb, ze = ranges[rank]

@@ -132,3 +132,19 @@ def test_balanced_slab_ranges():
     assert all(b - a >= 4 for a, b in rg) and rg[-1][1] == 64
     with pytest.raises(RuntimeError):
         parallel.balanced_slab_ranges(np.ones(16), 8)
+
+
+def test_rebalance_slab_ranges_equalises_measured_time():
+    from b200recon import parallel
+    R = 512
+    work = np.zeros(R)
+    work[50:200] = 1.0
+    true_cost = work.copy()
+    true_cost[50:80] *= 3.0            # a region whose voxels cost three times what the update count suggests
+    rg = parallel.balanced_slab_ranges(work, 4)
+    for _ in range(3):
+        times = [true_cost[a:b].sum() + 1e-9 for a, b in rg]
+        rg = parallel.rebalance_slab_ranges(rg, work, times)
+    times = np.array([true_cost[a:b].sum() for a, b in rg])
+    assert times.max() / times.mean() < 1.12, times
+    assert rg[0][0] == 0 and rg[-1][1] == R and all(rg[i][1] == rg[i + 1][0] for i in range(3))
