@@ -234,9 +234,9 @@ def run_gpu(args):
         probe = [(depth_f[k], exts[k]) for k in range(0, nf, max(1, nf // 16))]
         work = parallel.probe_plane_work(L, R, trunc, syn.volume_origin(L), probe, intr, probe_resolution=128, device=local)
         ranges = parallel.balanced_slab_ranges(work, world)
-        # two feedback steps: time the streaming kernel of every rank on its slab over 12 frames, rescale the work
+        # three feedback steps: time the streaming kernel of every rank on its slab over 12 frames, rescale the work
         # estimate of each slab to its measured time, cut again (setup, outside the timed region; one all_gather of a float)
-        for _ in range(2):
+        for _ in range(3):
             zb, ze = ranges[rank]
             v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
                                                             syn.volume_origin(L), z_range=(zb, ze), device=local)
