@@ -63,6 +63,28 @@ def compute(orc):
         out["icp_stats_%d" % kind] = np.array([r["fitness"], r["inlier_rmse"]])
         out["corr_sha1_%d" % kind] = _digest(r["corr"])
         out["iters_%d" % kind] = np.array([r["iterations"], r["n_corr"]], np.int64)
+    # --- point-cloud preprocessing (rows f1/f2) and colored ICP (f3)
+    import test_cloud_oracle_cpu as tco
+    P, N = tig.surface_cloud(3000, 7, 0.0002)
+    Cc = tco.texture(P)
+    dp, dn, dc = orc.voxel_down_sample(P, 0.01, N, Cc)
+    out["vds_count"] = np.array([len(dp)], np.int64)
+    out["vds_points_sha1"] = _digest(dp)
+    out["vds_colors_sha1"] = _digest(dc)
+    out["vds_first_points"] = dp[:6].copy()
+    nn = orc.estimate_normals(dp, orc.SEARCH_HYBRID, 0.03, 30)
+    out["normals_first"] = nn[:6].copy()
+    out["normals_sum"] = nn.sum(0)
+    idx, avg = orc.statistical_outlier(P, 20, 2.0)
+    out["outlier_kept_sha1"] = _digest(idx)
+    out["outlier_stats"] = np.array([len(idx), avg.mean()], np.float64)
+    g = orc.color_gradient(dp, nn, dc, 0.03, 30)
+    out["grad_first"] = g[:6].copy()
+    Ps2 = P @ Ti[:3, :3].T + Ti[:3, 3]
+    r = orc.registration_colored_icp(Ps2, Cc, P, N, Cc, 0.01, np.eye(4), 0.968, 1e-6, 1e-6, 50)
+    out["cicp_T"] = r["transformation"]
+    out["cicp_stats"] = np.array([r["fitness"], r["inlier_rmse"]])
+    out["cicp_iters"] = np.array([r["iterations"], r["n_corr"]], np.int64)
     return out
 
 
