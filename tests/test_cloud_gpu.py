@@ -160,3 +160,34 @@ def test_colored_icp_matches_oracle(o3d, orc):
         reg.registration_colored_icp(cloud(o3d, Ps), t, 0.01)
     with pytest.raises(RuntimeError):
         reg.registration_colored_icp(s, cloud(o3d, Pt, None, Ct), 0.01)
+
+
+def test_cloud_ops_small_and_degenerate_inputs(o3d, orc):
+    """fewer points than neighbours asked for, duplicates, empty clouds, a single point"""
+    g = o3d.geometry
+    rng = np.random.default_rng(5)
+    P = rng.uniform(-0.05, 0.05, size=(7, 3))
+    pc = cloud(o3d, P)
+    pc.estimate_normals(g.KDTreeSearchParamKNN(30))            # k > n: all 7 points are the neighbourhood
+    assert np.abs(np.asarray(pc.normals) - orc.estimate_normals(P, 0, 0.0, 30)).max() <= 1e-9
+    out, idx = pc.remove_statistical_outlier(20, 2.0)
+    ridx, _ = orc.statistical_outlier(P, 20, 2.0)
+    assert idx == ridx.tolist()
+    D = np.concatenate([P, P, P[:3]])                           # exact duplicates: ties broken by index
+    from b200recon import cloud_ops
+    i1, d1 = cloud_ops.knn_search(D, D, g.KDTreeSearchParamKNN(5))
+    i2, d2 = orc.knn(D, D, 0, 0.0, 5)
+    assert np.array_equal(i1, i2) and np.array_equal(d1, d2)
+    dd = cloud(o3d, D).voxel_down_sample(0.01)
+    rp, _, _ = orc.voxel_down_sample(D, 0.01)
+    assert np.array_equal(np.asarray(dd.points), rp)
+    one = cloud(o3d, P[:1])
+    one.estimate_normals(g.KDTreeSearchParamHybrid(0.1, 30))
+    assert np.array_equal(np.asarray(one.normals), [[0.0, 0.0, 1.0]])
+    e = g.PointCloud()
+    e.estimate_normals(g.KDTreeSearchParamHybrid(0.1, 30))
+    assert len(e.points) == 0
+    o, i = e.remove_statistical_outlier(20, 2.0)
+    assert len(o.points) == 0 and i == []
+    with pytest.raises(RuntimeError):
+        pc.estimate_normals(g.KDTreeSearchParamHybrid(0.1, 1000))   # max_nn beyond the 128-neighbour heap
