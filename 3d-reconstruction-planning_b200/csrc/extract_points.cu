@@ -70,10 +70,15 @@ __global__ void __launch_bounds__(PC_THREADS) pc_count2_kernel(const float2* __r
     const int64_t t = ((int64_t)blockIdx.x * PC_THREADS + threadIdx.x) * 2;
     unsigned c = 0;
     if (t < n) {
-        const int y = (int)(t % R), x = (int)((t / R) % R), z = G.z_begin + (int)(t / ((int64_t)R * R));
-        const float4 q = __ldcs(reinterpret_cast<const float4*>(tsdfw + pidx(R, G.z_begin, x, y, z)));
-        if (pc_valid(make_float2(q.x, q.y))) c += __popc(pc_flags(tsdfw, G, x, y, z));
-        if (pc_valid(make_float2(q.z, q.w))) c += __popc(pc_flags(tsdfw, G, x, y + 1, z));
+        // owned voxels are contiguous in memory behind the B2R_PAD_LO halo planes: the streaming load needs no
+        // index arithmetic; (x, y, z) are only worked out for the rare surface candidates
+        const float4 q = __ldcs(reinterpret_cast<const float4*>(tsdfw + (int64_t)B2R_PAD_LO * R * R + t));
+        const bool va = pc_valid(make_float2(q.x, q.y)), vb = pc_valid(make_float2(q.z, q.w));
+        if (va | vb) {
+            const int y = (int)(t % R), x = (int)((t / R) % R), z = G.z_begin + (int)(t / ((int64_t)R * R));
+            if (va) c += __popc(pc_flags(tsdfw, G, x, y, z));
+            if (vb) c += __popc(pc_flags(tsdfw, G, x, y + 1, z));
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);

