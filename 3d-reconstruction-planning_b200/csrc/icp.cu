@@ -21,6 +21,9 @@
 
 namespace b2r {
 
+#ifndef B2R_ICP_MINB
+#define B2R_ICP_MINB 6
+#endif
 constexpr int ICP_THREADS = 256;
 constexpr int ICP_PTS_PER_THREAD = 4;
 constexpr int ICP_NACC = 29;       // [0] count, [1] sum d^2, [2..28] estimation sums
@@ -375,7 +378,7 @@ __global__ void __launch_bounds__(256) icp_gather_color_kernel(const double* __r
 }
 
 template <int EST>
-__global__ void __launch_bounds__(ICP_THREADS, 3) icp_iterate_kernel(const __grid_constant__ IcpArgs A) {
+__global__ void __launch_bounds__(ICP_THREADS, B2R_ICP_MINB) icp_iterate_kernel(const __grid_constant__ IcpArgs A) {
     const int p = blockIdx.y;
     IcpState& St = A.states[p];
     if (St.done) return;
