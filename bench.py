@@ -38,7 +38,14 @@ WORKLOADS = {
     # name: (resolution, length m, sdf_trunc m, orbit frames, orbit radius m)   SURVEY.md 8(d)
     "tsdf512": (512, 1.024, 0.01, 64, 0.5),
     "tsdf1024": (1024, 2.048, 0.01, 256, 0.9),
+    "tsdf2048": (2048, 4.096, 0.01, 1000, 1.8),     # BASELINE config[4]: 1280x720 stream into 2048^3 (103 GB: 8 GPUs, or one)
 }
+CAMERAS = {"tsdf2048": "SYN_1280x720"}               # every other workload: the D435 640x480 intrinsics of stitcher.py:264-267
+
+
+def camera(workload):
+    from b200recon import synthetic as syn
+    return getattr(syn, CAMERAS.get(workload, "D435_640x480"))
 # dram__bytes_read.sum + dram__bytes_write.sum of one integrate_items launch from the committed ncu --set full
 # capture of this command (profiles/r01_integrate_v10_ncu.txt); per launch, like roofline.achieved
 NCU_TRAFFIC = {"tsdf1024": 881662208 + 702442752}
@@ -203,7 +210,7 @@ def run_gpu(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    K = syn.D435_640x480
+    K = camera(args.workload)
     kt = (K["fx"], K["fy"], K["cx"], K["cy"])
     intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], *kt)
     R, L, trunc, poses = orbit(args.workload)
@@ -342,7 +349,7 @@ def run_gpu(args):
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import bench_extra
         try:
-            extra["mesh"] = bench_extra.mesh_bench(vol) if world == 1 else None
+            extra["mesh"] = bench_extra.mesh_bench(vol) if (world == 1 and R <= 1024) else None
         except Exception as e:  # e.g. out of memory for the mesh of a very large volume: report, do not hide
             extra["mesh"] = {"error": str(e)}
         vol.reset()
@@ -365,12 +372,12 @@ def run_gpu(args):
         achieved = alg_bytes / (k_ms_timed / max(args.steps, 1) * 1e-3) / 1e9
         fps = args.steps / (ms * 1e-3)
         out = {
-            "metric": "TSDF integration frames/s (640x480 RGB-D into dense TSDF+colour volume)",
+            "metric": "TSDF integration frames/s (%dx%d RGB-D into dense TSDF+colour volume)" % (K["width"], K["height"]),
             "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "resolution": R, "voxel_mm": 1000.0 * L / R, "frames_in_orbit": len(poses),
-                       "frame": "640x480 uint16 depth + uint8 rgb", "sharding": "z-slab x%d" % world, "slab_boundaries": [a for a, _ in ranges] + [R],
+                       "frame": "%dx%d uint16 depth + uint8 rgb" % (K["width"], K["height"]), "sharding": "z-slab x%d" % world, "slab_boundaries": [a for a, _ in ranges] + [R],
                        "l2": "volume (%.1f GB) >> L2; consecutive frames touch overlapping voxels as in a real "
                              "sequence, no artificial flush" % (R ** 3 * 12 / 1e9)},
             "voxel_updates_per_s": upd / (ms * 1e-3),
@@ -423,8 +430,7 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
-    from b200recon import synthetic as syn
-    K = syn.D435_640x480
+    K = camera(args.workload)
 
     if args.impl == "reference":
         if rank != 0:
@@ -433,7 +439,7 @@ def main():
         cores = os.cpu_count()
         R = WORKLOADS[args.workload][0]
         emit(({
-            "impl": "reference", "metric": "TSDF integration frames/s (640x480 RGB-D into dense TSDF+colour volume)",
+            "impl": "reference", "metric": "TSDF integration frames/s (%dx%d RGB-D into dense TSDF+colour volume)" % (K["width"], K["height"]),
             "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": n, "warmup": args.warmup,
             "ms_per_step": 1000.0 / fps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": {"workload": args.workload, "resolution": R},
