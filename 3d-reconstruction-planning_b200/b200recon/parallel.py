@@ -78,6 +78,45 @@ def rebalance_slab_ranges(ranges, plane_work, times, min_planes=4):
     return balanced_slab_ranges(cost, len(ranges), min_planes)
 
 
+def profile_plane_cost(length, resolution, sdf_trunc, origin, frames, intrinsic, plane_work, chunk=32, color_type=None,
+                       device=None):
+    """Measured cost profile for `balanced_slab_ranges`: times the streaming kernel of `frames` -- an iterable of
+    (depth_f32 CUDA tensor, colour CUDA tensor or None, extrinsic) -- on every `chunk`-plane slab of the cube by itself,
+    subtracts the fixed per-launch floor (the cheapest slab) and spreads each slab's time over its planes in
+    proportion to `plane_work` (uniformly where the slab has no updates at all: planes under a surface are sampled and
+    rejected, which costs time but shows up in no update count).  Setup-time calibration, a second or two; every rank
+    measures the same profile on its own GPU, no collective."""
+    from . import runtime
+    from .pipelines import integration
+    R = int(resolution)
+    ct = integration.TSDFVolumeColorType.RGB8 if color_type is None else color_type
+    c = runtime.ctx(device)
+    t = runtime.torch()
+    w = np.maximum(np.asarray(plane_work, np.float64).reshape(-1), 0.0)
+    frames = list(frames)
+    times, slabs = [], []
+    for a in range(0, R, chunk):
+        b = min(R, a + chunk)
+        v = integration.UniformTSDFVolume(length, R, sdf_trunc, ct, origin, z_range=(a, b), device=device)
+        v.integrate_device(frames[0][0], frames[0][1], intrinsic, frames[0][2])       # warm-up (scratch allocation)
+        c.kernel_timing(True)
+        for d, col, ext in frames:
+            v.integrate_device(d, col, intrinsic, ext)
+        c.kernel_timing(False)
+        ms, n = c.kernel_time()
+        times.append(ms / max(n, 1))
+        slabs.append((a, b))
+        del v
+    t.cuda.empty_cache()
+    floor = min(times)
+    cost = np.zeros(R)
+    for (a, b), tm in zip(slabs, times):
+        ws = w[a:b].sum()
+        share = (w[a:b] / ws) if ws > 0 else np.full(b - a, 1.0 / (b - a))
+        cost[a:b] = max(tm - floor, 0.0) * share
+    return cost
+
+
 def probe_plane_work(length, resolution, sdf_trunc, origin, frames, intrinsic, probe_resolution=128, device=None):
     """Per-plane work estimate for `balanced_slab_ranges`: integrates `frames` -- an iterable of (depth_f32 CUDA
     tensor [H,W] in metres, extrinsic 4x4) -- into a coarse NoColor copy of the cube (probe_resolution^3, same

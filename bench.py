@@ -47,8 +47,8 @@ def camera(workload):
     from b200recon import synthetic as syn
     return getattr(syn, CAMERAS.get(workload, "D435_640x480"))
 # dram__bytes_read.sum + dram__bytes_write.sum of one integrate_items launch from the committed ncu --set full
-# capture of this command (profiles/r01_integrate_v10_ncu.txt); per launch, like roofline.achieved
-NCU_TRAFFIC = {"tsdf1024": 881662208 + 702442752}
+# capture of this command (profiles/r01_integrate_v11_ncu.txt); per launch, like roofline.achieved
+NCU_TRAFFIC = {"tsdf1024": 878633728 + 703095808}
 B_UPD = 24  # algorithmic bytes per voxel update: float2 R+W (16) + packed colour R+W (8)  
 
 
@@ -240,10 +240,13 @@ def run_gpu(args):
     if world > 1 and not args.equal_slabs:
         probe = [(depth_f[k], exts[k]) for k in range(0, nf, max(1, nf // 16))]
         work = parallel.probe_plane_work(L, R, trunc, syn.volume_origin(L), probe, intr, probe_resolution=128, device=local)
+        # measured cost per 32-plane slab (occluded planes under the table cost time without a single update)
+        cprobe = [(depth_f[k], rgb[k], exts[k]) for k in range(0, nf, max(1, nf // 8))]
+        work = parallel.profile_plane_cost(L, R, trunc, syn.volume_origin(L), cprobe, intr, work, chunk=32, device=local)
         ranges = parallel.balanced_slab_ranges(work, world)
-        # three feedback steps: time the streaming kernel of every rank on its slab over 12 frames, rescale the work
+        # one feedback step (the kernel times repeat to about +-5 %, more steps chase noise): time the streaming kernel of every rank on its slab over 12 frames, rescale the work
         # estimate of each slab to its measured time, cut again (setup, outside the timed region; one all_gather of a float)
-        for _ in range(3):
+        for _ in range(1):
             zb, ze = ranges[rank]
             v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
                                                             syn.volume_origin(L), z_range=(zb, ze), device=local)
