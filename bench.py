@@ -65,11 +65,16 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed regions.  nvidia-smi takes longer to start
+    than a short timed region lasts (256 steps on 8 GPUs = 22 ms), so one process runs across all timed passes of
+    the same load, every row is time-stamped when it arrives, and only rows that fall inside a timed window
+    (begin()/end() around the event-bracketed loop) are reported."""
 
-    def __init__(self, device):
+    def __init__(self, device, period_ms=20):
         self.device = device
-        self.rows = []
+        self.period_ms = period_ms
+        self.rows = []          # (monotonic time, fields)
+        self.windows = []       # [t0, t1]
         self.proc = None
 
     def start(self):
@@ -77,33 +82,43 @@ class ClockSampler:
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
+                                          "--format=csv,noheader,nounits", "-lms", str(self.period_ms)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
             return
         self.t = threading.Thread(target=self._read, daemon=True)
         self.t.start()
+        t_end = time.monotonic() + 3.0          # wait for the first row: the process is up and sampling
+        while not self.rows and time.monotonic() < t_end and self.proc.poll() is None:
+            time.sleep(0.01)
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.monotonic(), [c.strip() for c in line.split(",")]))
+
+    def begin(self):
+        self.windows.append([time.monotonic(), None])
+
+    def end(self):
+        self.windows[-1][1] = time.monotonic()
 
     def stop(self):
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        ok = [r for t, r in self.rows if len(r) >= 6 and any(a <= t <= (b or t) for a, b in self.windows)]
+        sm = [float(r[0]) for r in ok if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in ok if r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
+        reasons = sorted({names[i] for r in ok for i in range(4) if r[2 + i] == "Active"})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "timed_windows": len(self.windows),
+                "period_ms": self.period_ms}
 
 
 def orbit(workload):
@@ -296,14 +311,17 @@ def run_gpu(args):
         k = i % nf
         vol.integrate_host(d16_h[k], rgb_h[k], intr, exts[k])
 
-    def timed(step, steps, warmup, sample_clocks=False):
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+
+    def timed(step, steps, warmup):
         vol.reset()
         for i in range(warmup):
             step(i)
         barrier()
-        sampler = ClockSampler(local) if sample_clocks else None
-        if sampler:
-            sampler.start()
+        if rank == 0:
+            sampler.begin()
         upd0 = vol.updates()
         l0 = ctx.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -313,8 +331,9 @@ def run_gpu(args):
         ctx.join()          # the streaming kernels run on the library's side stream: e1 goes behind the last one
         e1.record()
         barrier()
+        if rank == 0:
+            sampler.end()
         ms = e0.elapsed_time(e1)
-        clocks = sampler.stop() if sampler else None
         upd = vol.updates() - upd0
         timed.local_updates = upd          # this rank's own share (roofline of rank 0's kernel)
         launches = ctx.launch_count() - l0
@@ -325,9 +344,9 @@ def run_gpu(args):
             u = torch.tensor([upd], dtype=torch.int64, device=dev)
             dist.all_reduce(u)
             upd = int(u.item())
-        return ms, upd, launches, clocks
+        return ms, upd, launches
 
-    ms, _, launches, clocks = timed(step_dev, args.steps, args.warmup, sample_clocks=True)
+    ms, _, launches = timed(step_dev, args.steps, args.warmup)
     # dominant kernel alone: CUDA events (on the stream it is launched on) around every integrate_items launch
     # of the same steps, run again
     ctx.kernel_timing(True)
@@ -340,9 +359,10 @@ def run_gpu(args):
     # voxel updates of exactly these steps: the same sequence replayed with the counting kernel variant (the
     # count is a deterministic function of the frame sequence since reset)
     vol.count_updates = True
-    _, upd, _, _ = timed(step_dev, args.steps, args.warmup)
+    _, upd, _ = timed(step_dev, args.steps, args.warmup)
     upd_k_local = timed.local_updates
-    e_ms, e_upd, _, _ = timed(step_e2e, args.steps, args.warmup)
+    e_ms, e_upd, _ = timed(step_e2e, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
     mirror = ctx.updates_mirror()
     assert mirror == vol.updates(), "host mirror of the step result disagrees with the device counter"
 
@@ -393,7 +413,7 @@ def run_gpu(args):
                             "the streaming kernel of frame i (library side stream)",
                     "voxel_updates_per_s": e_upd / (e_ms * 1e-3)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC.get(args.workload), "kernel": "integrate_items_kernel", "peak_source": peak_src,
+                         "traffic": NCU_TRAFFIC.get(args.workload) if world == 1 else None, "kernel": "integrate_items_kernel", "peak_source": peak_src,
                          "kernel_ms_per_launch": k_ms_timed / max(args.steps, 1),
                          "alg_bytes_per_launch": alg_bytes, "bytes_per_update": B_UPD,
                          "frac_of_nominal_8TBs": achieved / 8000.0},

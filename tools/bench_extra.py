@@ -28,7 +28,9 @@ def timed(fn, reps=1):
     torch.cuda.synchronize()
     e0, e1 = _ev(), _ev()
     e0.record()
+    out = None
     for _ in range(reps):
+        out = None          # drop the previous result first: its buffers go back to torch's cache instead of a fresh cudaMalloc
         out = fn()
     e1.record()
     torch.cuda.synchronize()
