@@ -66,6 +66,8 @@ SIGNATURES = {
     "b2r_integrate": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, C.POINTER(Intrinsic), c_dp, c_vp, c_vp]),
     "b2r_integrate_host": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, C.c_int, c_vp, C.POINTER(Intrinsic), c_dp,
                                      C.c_double, C.c_double, c_vp, c_vp]),
+    "b2r_integrate_units": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, C.POINTER(Intrinsic), c_dp, c_dp, C.c_int, C.c_int,
+                                      C.POINTER(C.c_int32), c_vp, C.c_int32, c_vp, c_vp, c_vp, c_vp]),
     "b2r_selftest_div": (C.c_int, [c_vp, C.c_int64, C.c_uint32, c_i64p, c_vp]),
     "b2r_volume_reset": (C.c_int, [c_vp, C.POINTER(Volume), c_vp]),
     "b2r_volume_export": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, c_vp, c_vp]),
@@ -76,6 +78,8 @@ SIGNATURES = {
     "b2r_extract_mesh_triangles": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp]),
     "b2r_extract_points_count": (C.c_int, [c_vp, C.POINTER(Volume), c_i64p, c_vp]),
     "b2r_extract_points_emit": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, c_vp, c_vp]),
+    "b2r_extract_points_emit_units": (C.c_int, [c_vp, C.POINTER(Volume), C.c_int, C.POINTER(C.c_int32), c_vp, c_vp, c_vp,
+                                                c_vp, c_vp]),
     "b2r_icp_batch": (C.c_int, [c_vp, C.c_int, c_vp, c_i64p, c_vp, c_vp, c_i64p, c_vp, c_vp, c_vp, c_dp,
                                 C.POINTER(IcpParams), C.POINTER(IcpResult), c_vp, c_vp]),
     "b2r_voxel_down_sample": (C.c_int, [c_vp, c_vp, c_vp, c_vp, C.c_int64, C.c_double, c_vp, c_vp, c_vp, c_i64p, c_vp]),

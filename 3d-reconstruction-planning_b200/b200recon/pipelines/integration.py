@@ -1,4 +1,5 @@
-"""`o3d.pipelines.integration`: UniformTSDFVolume on the B200 (north_star API).
+"""`o3d.pipelines.integration`: UniformTSDFVolume and ScalableTSDFVolume on the B200 (north_star API; SURVEY.md
+A.3/A.4, rows a5/a6/f4).
 
     vol = UniformTSDFVolume(length, resolution, sdf_trunc, color_type, origin)
     vol.integrate(rgbd, intrinsic, extrinsic)
@@ -225,3 +226,120 @@ class UniformTSDFVolume(TSDFVolume):
         if Cc is not None:
             pcd._c.set_dev(Cc)
         return pcd
+
+
+class ScalableTSDFVolume(UniformTSDFVolume):
+    """Open3D `ScalableTSDFVolume(voxel_length, sdf_trunc, color_type, volume_unit_resolution=16,
+    depth_sampling_stride=4)` (SURVEY.md A.3 last bullet, row f4): per frame only the 16^3-voxel units within
+    sdf_trunc of a (stride-4) depth sample are integrated, each with its own origin and its own float32 z-chain.
+
+    B200 design: the units are NOT hashed.  They live at their place in a dense backing cube in HBM (a unit that was
+    never opened holds weight 0, which every extraction rule of Open3D treats exactly like a missing unit), so mesh /
+    point extraction, persistence and the z-slab machinery are the dense kernels unchanged, and "scalable" is the
+    per-frame list of touched units (`b2r_integrate_units`).  Open3D's volume is unbounded; this one covers
+    `resolution`^3 voxels (multiple of the unit size) whose first unit is `unit_offset` (default: cube centred on the
+    world origin; `origin=` snaps down to a unit boundary).  Unit touches outside the cube are counted
+    (`units_clipped()`), never silently dropped.
+
+    Differences from Open3D: vertex / point order (memory order instead of hash-iteration order); voxels on the
+    outermost layer of the backing cube produce no points (the dense extraction's border rule)."""
+
+    def __init__(self, voxel_length, sdf_trunc, color_type=TSDFVolumeColorType.RGB8, volume_unit_resolution=16,
+                 depth_sampling_stride=4, *, resolution=512, origin=None, unit_offset=None, device=None):
+        self.volume_unit_resolution = int(volume_unit_resolution)
+        self.depth_sampling_stride = int(depth_sampling_stride)
+        ur = self.volume_unit_resolution
+        if not (1 <= ur <= 16):
+            raise RuntimeError("ScalableTSDFVolume: volume_unit_resolution must be in [1, 16] (got %d)" % ur)
+        if self.depth_sampling_stride < 1:
+            raise RuntimeError("ScalableTSDFVolume: depth_sampling_stride must be >= 1")
+        if int(resolution) % ur:
+            raise RuntimeError("ScalableTSDFVolume: resolution must be a multiple of volume_unit_resolution")
+        self.volume_unit_length = float(voxel_length) * ur
+        nu = int(resolution) // ur
+        if unit_offset is None:
+            if origin is None:
+                unit_offset = (-(nu // 2),) * 3
+            else:
+                unit_offset = tuple(int(np.floor(float(o) / self.volume_unit_length + 1e-9)) for o in origin)
+        self.unit_offset = np.ascontiguousarray(unit_offset, np.int32).reshape(3)
+        self.units_per_side = nu
+        super().__init__(float(voxel_length) * int(resolution), int(resolution), sdf_trunc, color_type,
+                         self.unit_offset.astype(np.float64) * self.volume_unit_length, device=device)
+        self.voxel_length = float(voxel_length)
+        self._desc.voxel_length = self.voxel_length          # exactly the constructor argument, not length / R
+        t = runtime.torch()
+        self._unit_stamp = t.zeros(nu ** 3, dtype=t.int32, device=self._ctx.tdev)
+        self._unit_list = t.empty(nu ** 3, dtype=t.int32, device=self._ctx.tdev)
+        self._unit_counters = t.zeros(4, dtype=t.int64, device=self._ctx.tdev)
+        self._frame_id = 0
+
+    def integrate_device(self, depth_f32, color, intrinsic, extrinsic):
+        c = self._ctx
+        E, ext = runtime.mat16(extrinsic)
+        P, pose = runtime.mat16(np.linalg.inv(E))      # Open3D: camera_pose = extrinsic.inverse(), float64
+        K = intrinsic._c()
+        upd = runtime.ptr(self._updates) if self.count_updates else C.c_void_p(0)
+        self._frame_id += 1
+        off = (C.c_int32 * 3)(*[int(v) for v in self.unit_offset])
+        _lib.check(_lib.load().b2r_integrate_units(
+            c.handle, C.byref(self._desc), runtime.ptr(depth_f32), runtime.ptr(color), C.byref(K), ext, pose,
+            self.volume_unit_resolution, self.depth_sampling_stride, off, runtime.ptr(self._unit_stamp),
+            self._frame_id, runtime.ptr(self._unit_list), runtime.ptr(self._unit_counters), upd, c.stream()))
+
+    def integrate_host(self, depth, color, intrinsic, extrinsic, depth_scale=1000.0, depth_trunc=3.0):
+        """Raw HOST frame -> H2D + Open3D's depth conversion + integrate (same contract as the uniform volume)."""
+        img = geometry.RGBDImage.create_from_color_and_depth(
+            geometry.Image(np.ascontiguousarray(color)) if color is not None else geometry.Image(np.zeros(depth.shape + (3,), np.uint8)),
+            geometry.Image(np.ascontiguousarray(depth)), depth_scale=depth_scale, depth_trunc=depth_trunc,
+            convert_rgb_to_intensity=False)
+        self.integrate(img, intrinsic, extrinsic)
+
+    def extract_point_cloud_device(self):
+        """ScalableTSDFVolume::ExtractPointCloud: world-coordinate interpolation from the unit origins and the
+        scalable GetTSDFAt for the normals (`b2r_extract_points_emit_units`)."""
+        c = self._ctx
+        t = runtime.torch()
+        n = C.c_int64(0)
+        _lib.check(_lib.load().b2r_extract_points_count(c.handle, C.byref(self._desc), C.byref(n), c.stream()))
+        n = n.value
+        P = t.empty((n, 3), dtype=t.float64, device=c.tdev)
+        N = t.empty((n, 3), dtype=t.float64, device=c.tdev)
+        Cc = t.empty((n, 3), dtype=t.float64, device=c.tdev) if self._color is not None else None
+        off = (C.c_int32 * 3)(*[int(v) for v in self.unit_offset])
+        _lib.check(_lib.load().b2r_extract_points_emit_units(
+            c.handle, C.byref(self._desc), self.volume_unit_resolution, off, runtime.ptr(self._unit_stamp),
+            runtime.ptr(P), runtime.ptr(N), runtime.ptr(Cc), c.stream()))
+        return P, N, Cc
+
+    def reset(self):
+        super().reset()
+        self._unit_stamp.zero_()
+        self._unit_counters.zero_()
+        self._frame_id = 0
+
+    # -- unit bookkeeping (device counters, read on demand: integrate itself never synchronises)
+    def _counters(self):
+        self._ctx.join()
+        return [int(v) for v in self._unit_counters.cpu().tolist()]
+
+    def units_touched_last_frame(self):
+        return self._counters()[0]
+
+    def units_clipped(self):
+        """unit touches that fell outside the backing cube so far (Open3D would have opened those units)"""
+        return self._counters()[1]
+
+    def units_opened(self):
+        return self._counters()[2]
+
+    def unit_keys(self):
+        """global integer indices of the opened units, int32 [n, 3] (Open3D's volume_units_ keys)"""
+        self._ctx.join()
+        nu = self.units_per_side
+        lin = runtime.torch().nonzero(self._unit_stamp).flatten().cpu().numpy()
+        k = np.stack([lin // (nu * nu), (lin // nu) % nu, lin % nu], 1).astype(np.int32)
+        return k + self.unit_offset[None, :]
+
+    def save(self, path):
+        raise NotImplementedError("ScalableTSDFVolume.save: persist through export_arrays()/unit_keys()")

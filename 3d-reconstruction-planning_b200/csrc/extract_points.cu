@@ -14,6 +14,11 @@ struct PcGeom {
     int R, z_begin, z_end;
     double vl, ox, oy, oz;
     int color_type;
+    // ScalableTSDFVolume mode (unit_res > 0): Open3D computes positions from the unit's own origin + in-unit index
+    // and GetTSDFAt returns 0 when the unit holding the sample's base voxel was never opened
+    int unit_res, nu, uoff[3];
+    double unit_len;
+    const int* unit_stamp;
 };
 
 __device__ __forceinline__ int64_t pidx(int R, int z_begin, int x, int y, int z) {
@@ -127,6 +132,37 @@ __device__ __forceinline__ double tsdf_at(const float2* __restrict__ tsdfw, cons
            r[0] * ((1 - r[1]) * ((1 - r[2]) * t100 + r[2] * t101) + r[1] * ((1 - r[2]) * t110 + r[2] * t111));
 }
 
+// Open3D ScalableTSDFVolume::GetTSDFAt(p), p in WORLD coordinates: the unit and the in-unit voxel of
+// p - vl/2 are located separately (index clamped into the unit), a missing base unit reads 0, neighbours in
+// missing units read 0 (the dense cube holds zeros there).
+__device__ __forceinline__ double tsdf_at_units(const float2* __restrict__ tsdfw, const PcGeom& G, const double* p) {
+    int idx[3];
+    double r[3];
+    int u[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double pl = p[k] - 0.5 * G.vl;
+        const int index0 = (int)floor(pl / G.unit_len);
+        const double g = (pl - (double)index0 * G.unit_len) / G.vl;
+        int i0 = (int)floor(g);
+        i0 = max(0, min(G.unit_res - 1, i0));
+        r[k] = g - (double)i0;
+        u[k] = index0 - G.uoff[k];
+        idx[k] = u[k] * G.unit_res + i0;
+    }
+    if ((unsigned)u[0] >= (unsigned)G.nu || (unsigned)u[1] >= (unsigned)G.nu || (unsigned)u[2] >= (unsigned)G.nu) return 0.0;
+    if (__ldg(&G.unit_stamp[(u[0] * G.nu + u[1]) * G.nu + u[2]]) == 0) return 0.0;
+    const int R = G.R;
+    auto T = [&](int dx, int dy, int dz) -> double {
+        const int x = idx[0] + dx, y = idx[1] + dy, z = idx[2] + dz;
+        if (x >= R || y >= R || z >= R) return 0.0;      // the neighbouring unit lies outside the cube: missing
+        return (double)__ldg(&tsdfw[pidx(R, G.z_begin, x, y, z)]).x;
+    };
+    return (1 - r[0]) * ((1 - r[1]) * ((1 - r[2]) * T(0, 0, 0) + r[2] * T(0, 0, 1)) + r[1] * ((1 - r[2]) * T(0, 1, 0) + r[2] * T(0, 1, 1))) +
+           r[0] * ((1 - r[1]) * ((1 - r[2]) * T(1, 0, 0) + r[2] * T(1, 0, 1)) + r[1] * ((1 - r[2]) * T(1, 1, 0) + r[2] * T(1, 1, 1)));
+}
+
+template <bool UNITS>
 __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __restrict__ tsdfw,
                                                              const uint32_t* __restrict__ color,
                                                              const __grid_constant__ PcGeom G,
@@ -155,7 +191,13 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
     const double hvl = 0.5 * G.vl;
     const int64_t i0 = pidx(R, G.z_begin, x, y, z);
     const float f0 = tsdfw[i0].x;
-    const double p0[3] = {hvl + G.vl * (double)x, hvl + G.vl * (double)y, hvl + G.vl * (double)z};
+    double p0[3] = {hvl + G.vl * (double)x, hvl + G.vl * (double)y, hvl + G.vl * (double)z};
+    if (UNITS) {     // (hvl + vl * in-unit index) + index.cast<double>() * unit_length, world coordinates
+        const int c[3] = {x, y, z};
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            p0[q] = (hvl + G.vl * (double)(c[q] % G.unit_res)) + (double)(G.uoff[q] + c[q] / G.unit_res) * G.unit_len;
+    }
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
         if (!(f & (1u << a))) continue;
@@ -165,9 +207,9 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
         double p[3] = {p0[0], p0[1], p0[2]};
         const double p1a = p0[a] + G.vl;
         p[a] = (p0[a] * (double)r1 + p1a * (double)r0) / (double)(r0 + r1);
-        pts[k * 3 + 0] = p[0] + G.ox;
-        pts[k * 3 + 1] = p[1] + G.oy;
-        pts[k * 3 + 2] = p[2] + G.oz;
+        pts[k * 3 + 0] = UNITS ? p[0] : p[0] + G.ox;
+        pts[k * 3 + 1] = UNITS ? p[1] : p[1] + G.oy;
+        pts[k * 3 + 2] = UNITS ? p[2] : p[2] + G.oz;
         if (cols && G.color_type) {
             const uint32_t c0 = color[i0], c1 = color[i1];
 #pragma unroll
@@ -190,9 +232,9 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
         for (int q = 0; q < 3; ++q) {
             double pp[3] = {p[0], p[1], p[2]};
             pp[q] -= half_gap;
-            const double t0 = tsdf_at(tsdfw, G, pp);
+            const double t0 = UNITS ? tsdf_at_units(tsdfw, G, pp) : tsdf_at(tsdfw, G, pp);
             pp[q] += 2 * half_gap;
-            const double t1 = tsdf_at(tsdfw, G, pp);
+            const double t1 = UNITS ? tsdf_at_units(tsdfw, G, pp) : tsdf_at(tsdfw, G, pp);
             nv[q] = t1 - t0;
         }
         const double nn = sqrt(nv[0] * nv[0] + nv[1] * nv[1] + nv[2] * nv[2]);
@@ -247,24 +289,46 @@ int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_poi
     return 0;
 }
 
-int b2r_extract_points_emit(b2r_ctx* ctx, const b2r_volume* vol, double* d_points, double* d_normals,
-                            double* d_colors, void* stream) {
-    B2R_CHECK(ctx && vol && vol->d_tsdfw, -1, "b2r_extract_points_emit: NULL argument");
+static int points_emit(b2r_ctx* ctx, const b2r_volume* vol, int unit_res, const int32_t* unit_offset, const int32_t* d_unit_stamp,
+                       double* d_points, double* d_normals, double* d_colors, void* stream) {
     B2R_CUDA(cudaSetDevice(ctx->device));
     const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
     if (nz <= 0 || R < 3 || ctx->pc_n == 0) return 0;
     B2R_CHECK(d_points && d_normals, -1, "b2r_extract_points_emit: NULL output");
     const int64_t n = (int64_t)nz * R * R;
     const int nblocks = cdiv(n, PC_THREADS);
-    PcGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
-             vol->color_type};
-    pc_emit_kernel<<<ctx->sm_count * 8, PC_THREADS, 0, S(stream)>>>((const float2*)vol->d_tsdfw, (const uint32_t*)vol->d_color, G,
-                                                          (const uint32_t*)ctx->pc_block_counts.ptr,
-                                                          (const uint32_t*)ctx->pc_block_counts.ptr + 3 * (size_t)nblocks,
-                                                          (const unsigned long long*)ctx->small.ptr + SMALL_PC_NLIVE, d_points,
-                                                          d_normals, vol->color_type ? d_colors : nullptr);
+    PcGeom G;
+    G.R = R; G.z_begin = vol->z_begin; G.z_end = vol->z_end; G.vl = vol->voxel_length;
+    G.ox = vol->origin[0]; G.oy = vol->origin[1]; G.oz = vol->origin[2]; G.color_type = vol->color_type;
+    G.unit_res = unit_res; G.nu = unit_res ? R / unit_res : 0; G.unit_len = vol->voxel_length * unit_res;
+    for (int a = 0; a < 3; ++a) G.uoff[a] = unit_offset ? unit_offset[a] : 0;
+    G.unit_stamp = d_unit_stamp;
+    const float2* tw = (const float2*)vol->d_tsdfw;
+    const uint32_t* col = (const uint32_t*)vol->d_color;
+    const uint32_t* blk = (const uint32_t*)ctx->pc_block_counts.ptr;
+    const unsigned long long* nlive = (const unsigned long long*)ctx->small.ptr + SMALL_PC_NLIVE;
+    double* dc = vol->color_type ? d_colors : nullptr;
+    if (unit_res)
+        pc_emit_kernel<true><<<ctx->sm_count * 8, PC_THREADS, 0, S(stream)>>>(tw, col, G, blk, blk + 3 * (size_t)nblocks, nlive, d_points, d_normals, dc);
+    else
+        pc_emit_kernel<false><<<ctx->sm_count * 8, PC_THREADS, 0, S(stream)>>>(tw, col, G, blk, blk + 3 * (size_t)nblocks, nlive, d_points, d_normals, dc);
     B2R_LAUNCH_CHECK(ctx);
     return 0;
+}
+
+int b2r_extract_points_emit(b2r_ctx* ctx, const b2r_volume* vol, double* d_points, double* d_normals,
+                            double* d_colors, void* stream) {
+    B2R_CHECK(ctx && vol && vol->d_tsdfw, -1, "b2r_extract_points_emit: NULL argument");
+    return points_emit(ctx, vol, 0, nullptr, nullptr, d_points, d_normals, d_colors, stream);
+}
+
+int b2r_extract_points_emit_units(b2r_ctx* ctx, const b2r_volume* vol, int unit_resolution, const int32_t* unit_offset,
+                                  const int32_t* d_unit_stamp, double* d_points, double* d_normals, double* d_colors,
+                                  void* stream) {
+    B2R_CHECK(ctx && vol && vol->d_tsdfw && unit_offset && d_unit_stamp, -1, "b2r_extract_points_emit_units: NULL argument");
+    B2R_CHECK(unit_resolution >= 1 && vol->resolution % unit_resolution == 0 && vol->z_begin == 0 && vol->z_end == vol->resolution,
+              -6, "b2r_extract_points_emit_units: whole cube of whole units expected");
+    return points_emit(ctx, vol, unit_resolution, unit_offset, d_unit_stamp, d_points, d_normals, d_colors, stream);
 }
 
 }  // extern "C"

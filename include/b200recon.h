@@ -107,6 +107,25 @@ int b2r_integrate(b2r_ctx* ctx, const b2r_volume* vol, const float* d_depth, con
 int b2r_integrate_host(b2r_ctx* ctx, const b2r_volume* vol, const void* h_depth, int depth_dtype,
                        const uint8_t* h_color, const b2r_intrinsic* K, const double* extrinsic, double depth_scale,
                        double depth_trunc, unsigned long long* d_updates, void* stream);
+/* O3D pipelines.integration.ScalableTSDFVolume.integrate(rgbd, intrinsic, extrinsic) -- SURVEY.md section 8 row f4
+ * / A.3 last bullet (Open3D 0.18 ScalableTSDFVolume::Integrate; no call site in the reference, named by
+ * north_star next to UniformTSDFVolume).  Open3D's hash of unit_resolution^3-voxel units is laid out at its place
+ * in a DENSE backing cube (`vol`, whole cube, origin = unit_offset * unit_length): a unit that was never opened
+ * reads weight 0 like a missing hash entry, so extraction is b2r_extract_mesh_* / b2r_extract_points_* unchanged.
+ * Per call: depth samples at `stride` are back-projected with camera_pose (= extrinsic^-1, float64, inverted by
+ * the caller), every unit between LocateVolumeUnit(p - sdf_trunc) and LocateVolumeUnit(p + sdf_trunc) is stamped
+ * with frame_id (>= 1, increasing) and integrated once with Open3D's per-unit arithmetic (column start from the
+ * unit's own origin, float32 z-chain restarted per unit).
+ *   d_unit_stamp  int32 [(R/unit_resolution)^3], zero before the first frame / after reset: 0 = unit not opened
+ *   d_unit_list   int32 scratch of the same size (the frame's touched units)
+ *   d_counters    uint64 [4] device: [0] units touched by this call, [1] unit touches that fell outside the
+ *                 cube (running total -- Open3D would have opened those units), [2] units opened so far
+ * No host synchronisation; everything runs on `stream` behind any b2r_integrate* still streaming. */
+int b2r_integrate_units(b2r_ctx* ctx, const b2r_volume* vol, const float* d_depth, const void* d_color,
+                        const b2r_intrinsic* K, const double* extrinsic, const double* camera_pose, int unit_resolution,
+                        int stride, const int32_t* unit_offset, int32_t* d_unit_stamp, int32_t frame_id,
+                        int32_t* d_unit_list, unsigned long long* d_counters, unsigned long long* d_updates,
+                        void* stream);
 /* Device self-test (blocking): the integrate kernel computes Open3D's IEEE float32 divisions with a shared
  * refined reciprocal; this runs n pseudo-random cases (projection-like, full-range, running-mean-like and
  * near-half-way quotients) through that code and through the `/` operator; mismatches[4] = count per family. */
@@ -142,6 +161,14 @@ int b2r_extract_mesh_triangles(b2r_ctx* ctx, const b2r_volume* vol, int32_t* d_t
 int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_points, void* stream); /* blocking */
 int b2r_extract_points_emit(b2r_ctx* ctx, const b2r_volume* vol, double* d_points, double* d_normals,
                             double* d_colors, void* stream);
+/* ScalableTSDFVolume.extract_point_cloud() on the dense backing cube of b2r_integrate_units (after
+ * b2r_extract_points_count on the same volume): positions are interpolated in WORLD coordinates from the unit's own
+ * origin + in-unit index, as Open3D's ScalableTSDFVolume::ExtractPointCloud does (its formula is not translation
+ * invariant: (p0*r1 + p1*r0) / float(r0 + r1)), and the normals use ScalableTSDFVolume::GetTSDFAt (0 when the unit
+ * of the sample's base voxel was never opened: d_unit_stamp == 0). */
+int b2r_extract_points_emit_units(b2r_ctx* ctx, const b2r_volume* vol, int unit_resolution, const int32_t* unit_offset,
+                                  const int32_t* d_unit_stamp, double* d_points, double* d_normals, double* d_colors,
+                                  void* stream);
 
 /* ---- ICP (O3D pipelines.registration.registration_icp, stitcher.py:94-110) ---------------- */
 /* Batched: pair p uses source points [src_off[p], src_off[p+1]) and target points

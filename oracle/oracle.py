@@ -49,6 +49,23 @@ def lib():
                                            C.c_double, C.c_double, C.c_double, C.c_double, c_dp]
         L.orc_volume_extract_mesh.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         L.orc_volume_extract_points.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+        L.orc_scalable_create.restype = C.c_void_p
+        L.orc_scalable_create.argtypes = [C.c_double, C.c_double, C.c_int, C.c_int, C.c_int]
+        for n in ("orc_scalable_destroy", "orc_scalable_reset"):
+            getattr(L, n).argtypes = [C.c_void_p]
+        L.orc_scalable_num_units.restype = C.c_int64
+        L.orc_scalable_num_units.argtypes = [C.c_void_p]
+        L.orc_scalable_unit_keys.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_scalable_unit_arrays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_scalable_integrate.restype = C.c_int64
+        L.orc_scalable_integrate.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double,
+                                             C.c_double, C.c_double, c_dp, c_dp, C.POINTER(C.c_int64)]
+        L.orc_scalable_extract_mesh.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.orc_scalable_extract_points.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+        for n, rt in (("orc_scalable_vertices", c_dp), ("orc_scalable_vertex_colors", c_dp),
+                      ("orc_scalable_normals", c_dp), ("orc_scalable_triangles", C.POINTER(C.c_int32))):
+            getattr(L, n).restype = rt
+            getattr(L, n).argtypes = [C.c_void_p]
         L.orc_depth_to_float.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_void_p]
         L.orc_distance_multiplier.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_void_p]
         L.orc_backproject.restype = C.c_int64
@@ -199,6 +216,106 @@ class UniformTSDFVolume:
 
 
 # ---------------------------------------------------------------------------------- ICP
+class ScalableTSDFVolume:
+    """Open3D ScalableTSDFVolume restated (scalable_oracle.cpp): a hash of unit_resolution^3 uniform units."""
+
+    def __init__(self, voxel_length, sdf_trunc, color_type=1, volume_unit_resolution=16, depth_sampling_stride=4):
+        self.voxel_length = float(voxel_length)
+        self.sdf_trunc = float(sdf_trunc)
+        self.color_type = int(color_type)
+        self.res = int(volume_unit_resolution)
+        self.stride = int(depth_sampling_stride)
+        self._h = C.c_void_p(lib().orc_scalable_create(self.voxel_length, self.sdf_trunc, self.color_type, self.res,
+                                                        self.stride))
+        self.touched = 0
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_scalable_destroy(self._h)
+            self._h = None
+
+    def reset(self):
+        lib().orc_scalable_reset(self._h)
+
+    def integrate(self, depth_f32, color, K, extrinsic):
+        depth_f32 = np.ascontiguousarray(depth_f32, np.float32)
+        H, W = depth_f32.shape
+        if color is not None:
+            color = np.ascontiguousarray(color)
+        ext = np.ascontiguousarray(extrinsic, np.float64)
+        pose = np.ascontiguousarray(np.linalg.inv(ext))     # the product's host does the same inversion
+        t = C.c_int64(0)
+        n = lib().orc_scalable_integrate(self._h, _vp(depth_f32), _vp(color), H, W, K[0], K[1], K[2], K[3], _dp(ext),
+                                         _dp(pose), C.byref(t))
+        if n < 0:
+            raise RuntimeError("oracle scalable integrate failed: %d" % n)
+        self.touched = t.value
+        return int(n)
+
+    def unit_keys(self):
+        n = lib().orc_scalable_num_units(self._h)
+        out = np.zeros((n, 3), np.int32)
+        if n:
+            lib().orc_scalable_unit_keys(self._h, _vp(out))
+        return out
+
+    def unit_arrays(self, key):
+        """(tsdf, weight, color|None) of one unit in Open3D order [x, y, z]."""
+        r = self.res
+        key = np.ascontiguousarray(key, np.int32)
+        ts, w = np.zeros((r, r, r), np.float32), np.zeros((r, r, r), np.float32)
+        col = np.zeros((r, r, r, 3), np.float64) if self.color_type else None
+        rc = lib().orc_scalable_unit_arrays(self._h, _vp(key), _vp(ts), _vp(w), _vp(col))
+        if rc:
+            raise KeyError(tuple(key))
+        return ts, w, col
+
+    def dense_arrays(self, unit_offset, n_units):
+        """The units inside the box of n_units^3 units starting at unit_offset, laid out as one dense cube
+        [x, y, z] (zeros where no unit exists); also returns the number of opened units outside the box."""
+        r, R = self.res, self.res * int(n_units)
+        ts, w = np.zeros((R, R, R), np.float32), np.zeros((R, R, R), np.float32)
+        col = np.zeros((R, R, R, 3), np.float64) if self.color_type else None
+        outside = 0
+        for k in self.unit_keys():
+            l = k - np.asarray(unit_offset)
+            if (l < 0).any() or (l >= n_units).any():
+                outside += 1
+                continue
+            a, b, c = (l * r).tolist()
+            t1, w1, c1 = self.unit_arrays(k)
+            ts[a:a + r, b:b + r, c:c + r] = t1
+            w[a:a + r, b:b + r, c:c + r] = w1
+            if col is not None:
+                col[a:a + r, b:b + r, c:c + r] = c1
+        return ts, w, col, outside
+
+    def extract_triangle_mesh(self):
+        nv, nt = C.c_int64(0), C.c_int64(0)
+        assert lib().orc_scalable_extract_mesh(self._h, C.byref(nv), C.byref(nt)) == 0
+        nv, nt = nv.value, nt.value
+        V = np.ctypeslib.as_array(lib().orc_scalable_vertices(self._h), (nv * 3,)).reshape(nv, 3).copy() if nv else np.zeros((0, 3))
+        T = np.ctypeslib.as_array(lib().orc_scalable_triangles(self._h), (nt * 3,)).reshape(nt, 3).copy() if nt else np.zeros((0, 3), np.int32)
+        Cc = None
+        if self.color_type != 0:
+            Cc = np.ctypeslib.as_array(lib().orc_scalable_vertex_colors(self._h), (nv * 3,)).reshape(nv, 3).copy() if nv else np.zeros((0, 3))
+        return V, T, Cc
+
+    def extract_point_cloud(self):
+        n = C.c_int64(0)
+        assert lib().orc_scalable_extract_points(self._h, C.byref(n)) == 0
+        n = n.value
+        if n == 0:
+            z = np.zeros((0, 3))
+            return z, z.copy(), (None if self.color_type == 0 else z.copy())
+        P = np.ctypeslib.as_array(lib().orc_scalable_vertices(self._h), (n * 3,)).reshape(n, 3).copy()
+        N = np.ctypeslib.as_array(lib().orc_scalable_normals(self._h), (n * 3,)).reshape(n, 3).copy()
+        Cc = None
+        if self.color_type != 0:
+            Cc = np.ctypeslib.as_array(lib().orc_scalable_vertex_colors(self._h), (n * 3,)).reshape(n, 3).copy()
+        return P, N, Cc
+
+
 def registration_icp(src, tgt, tgt_normals, max_dist, init=None, kind=1, rel_fitness=1e-6, rel_rmse=1e-6,
                      max_iter=30):
     """A.5.  kind 0 = point-to-point, 1 = point-to-plane.  Returns dict."""

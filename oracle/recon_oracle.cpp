@@ -24,7 +24,7 @@
 #include <unordered_map>
 #include <vector>
 
-#include "mc_tables.inc"
+#include "recon_internal.h"
 
 extern "C" {
 
@@ -109,19 +109,6 @@ int64_t orc_backproject(const float* depth, const uint8_t* color, int nc, int H,
 // without allocating all of it -- Open3D parallelises Integrate over x, so an x-range is the
 // natural sample.  IndexOf(x,y,z) = x*R*R + y*R + z (z fastest), as Open3D.
 // ------------------------------------------------------------------------------------------
-struct OrcVolume {
-    double length, voxel_length, sdf_trunc, origin[3];
-    int R, color_type;  // 0 NoColor, 1 RGB8, 2 Gray32
-    int x_begin, x_end;
-    std::vector<float> tsdf, weight;
-    std::vector<double> color;  // 3 per voxel (RGB8) / 1 used (Gray32)
-    // extraction results
-    std::vector<double> verts, vcols, normals;
-    std::vector<int32_t> tris;
-    inline int64_t idx(int x, int y, int z) const {
-        return ((int64_t)(x - x_begin) * R + y) * R + z;
-    }
-};
 
 void* orc_volume_create(double length, int resolution, double sdf_trunc, int color_type,
                         const double* origin, int x_begin, int x_end) {
@@ -161,7 +148,77 @@ void orc_distance_multiplier(int H, int W, double fx, double fy, double cx, doub
             out[(int64_t)i * W + j] = sqrtf(xx[j] * xx[j] + yy[i] * yy[i] + 1.0f);
 }
 
-// UniformTSDFVolume::Integrate -> IntegrateWithDepthToCameraDistanceMultiplier.
+// UniformTSDFVolume::IntegrateWithDepthToCameraDistanceMultiplier, the columns of ONE x index (the body of
+// Open3D's `omp parallel for` over x).  Shared by the uniform volume and by the 16^3 units of the scalable one.
+
+void make_frame(IntegrateFrame& F, const OrcVolume* vol, const float* depth, const void* color, const float* mult,
+                       int H, int W, double fx_d, double fy_d, double cx_d, double cy_d, const double* extrinsic) {
+    F.depth = depth; F.color = color; F.mult = mult; F.H = H; F.W = W;
+    F.fx = (float)fx_d; F.fy = (float)fy_d; F.cx = (float)cx_d; F.cy = (float)cy_d;
+    F.vl = (float)vol->voxel_length;
+    F.hvl = F.vl * 0.5f;
+    F.trunc = (float)vol->sdf_trunc;
+    F.trunc_inv = 1.0f / F.trunc;
+    for (int r = 0; r < 4; ++r)
+        for (int c = 0; c < 4; ++c) { F.E[r][c] = (float)extrinsic[r * 4 + c]; F.Es[r][c] = F.E[r][c] * F.vl; }
+    F.safe_w = (float)W - 0.0001f; F.safe_h = (float)H - 0.0001f;
+}
+
+int64_t integrate_x(OrcVolume* vol, const IntegrateFrame& F, int x) {
+    const float fx = F.fx, fy = F.fy, cx = F.cx, cy = F.cy, vl = F.vl, hvl = F.hvl, trunc = F.trunc, trunc_inv = F.trunc_inv;
+    const float safe_w = F.safe_w, safe_h = F.safe_h;
+    const float* depth = F.depth; const float* mult = F.mult;
+    const int W = F.W, R = vol->R;
+    const uint8_t* rgb8 = (const uint8_t*)F.color;
+    const float* gray = (const float*)F.color;
+    int64_t updates = 0;
+    for (int y = 0; y < R; ++y) {
+        // pt_3d_homo(float(hvl + vl*x + origin_(0)), ...): the float sum is promoted to
+        // double by origin_ (Vector3d) and rounded back to float.
+        const float px = (float)((double)(hvl + vl * (float)x) + vol->origin[0]);
+        const float py = (float)((double)(hvl + vl * (float)y) + vol->origin[1]);
+        const float pz = (float)((double)hvl + vol->origin[2]);
+        // Eigen 4x4 * 4x1 float, coefficient-based lazy product, column-major packets:
+        // ((col0*x + col1*y) + col2*z) + col3*1, separate mul/add roundings (no FMA).
+        float pc[3];
+        for (int r = 0; r < 3; ++r)
+            pc[r] = ((F.E[r][0] * px + F.E[r][1] * py) + F.E[r][2] * pz) + F.E[r][3] * 1.0f;
+        for (int z = 0; z < R; ++z, pc[0] += F.Es[0][2], pc[1] += F.Es[1][2], pc[2] += F.Es[2][2]) {
+            if (pc[2] <= 0) continue;
+            const float u_f = pc[0] * fx / pc[2] + cx + 0.5f;
+            const float v_f = pc[1] * fy / pc[2] + cy + 0.5f;
+            if (!(u_f >= 0.0001f && u_f < safe_w && v_f >= 0.0001f && v_f < safe_h)) continue;
+            const int u = (int)u_f, v = (int)v_f;
+            const float d = depth[(int64_t)v * W + u];
+            if (d <= 0.0f) continue;
+            const float sdf = (d - pc[2]) * mult[(int64_t)v * W + u];
+            if (sdf > -trunc) {
+                const float tsdf = std::min(1.0f, sdf * trunc_inv);
+                const int64_t i = vol->idx(x, y, z);
+                const float w = vol->weight[i];
+                vol->tsdf[i] = (vol->tsdf[i] * w + tsdf) / (w + 1.0f);
+                if (vol->color_type == 1) {
+                    const uint8_t* p = rgb8 + ((int64_t)v * W + u) * 3;
+                    double* c = &vol->color[i * 3];
+                    const double wd = (double)w, w1 = (double)(w + 1.0f);
+                    c[0] = (c[0] * wd + (double)p[0]) / w1;
+                    c[1] = (c[1] * wd + (double)p[1]) / w1;
+                    c[2] = (c[2] * wd + (double)p[2]) / w1;
+                } else if (vol->color_type == 2) {
+                    double* c = &vol->color[i * 3];
+                    const double g = (double)gray[(int64_t)v * W + u];
+                    const double wd = (double)w, w1 = (double)(w + 1.0f);
+                    c[0] = (c[0] * wd + g) / w1; c[1] = c[0]; c[2] = c[0];
+                }
+                vol->weight[i] = w + 1.0f;
+                ++updates;
+            }
+        }
+    }
+    return updates;
+}
+
+// UniformTSDFVolume::Integrate.
 // depth: float32 metres [H,W]; color: uint8 [H,W,3] (RGB8) or float32 [H,W] (Gray32) or NULL.
 // Returns the number of voxel updates performed (for the voxel-updates/s metric), <0 on error.
 int64_t orc_volume_integrate(void* h, const float* depth, const void* color, int H, int W,
@@ -171,67 +228,11 @@ int64_t orc_volume_integrate(void* h, const float* depth, const void* color, int
     if (vol->color_type != 0 && !color) return -2;
     std::vector<float> mult((size_t)H * W);
     orc_distance_multiplier(H, W, fx_d, fy_d, cx_d, cy_d, mult.data());
-
-    const float fx = (float)fx_d, fy = (float)fy_d, cx = (float)cx_d, cy = (float)cy_d;
-    float E[4][4], Es[4][4];
-    const float vl = (float)vol->voxel_length;
-    const float hvl = vl * 0.5f;
-    const float trunc = (float)vol->sdf_trunc;
-    const float trunc_inv = 1.0f / trunc;
-    for (int r = 0; r < 4; ++r)
-        for (int c = 0; c < 4; ++c) { E[r][c] = (float)extrinsic[r * 4 + c]; Es[r][c] = E[r][c] * vl; }
-    const float safe_w = (float)W - 0.0001f, safe_h = (float)H - 0.0001f;
-    const int R = vol->R;
-    const uint8_t* rgb8 = (const uint8_t*)color;
-    const float* gray = (const float*)color;
+    IntegrateFrame F;
+    make_frame(F, vol, depth, color, mult.data(), H, W, fx_d, fy_d, cx_d, cy_d, extrinsic);
     int64_t updates = 0;
-
 #pragma omp parallel for schedule(static) reduction(+ : updates)
-    for (int x = vol->x_begin; x < vol->x_end; ++x) {
-        for (int y = 0; y < R; ++y) {
-            // pt_3d_homo(float(hvl + vl*x + origin_(0)), ...): the float sum is promoted to
-            // double by origin_ (Vector3d) and rounded back to float.
-            const float px = (float)((double)(hvl + vl * (float)x) + vol->origin[0]);
-            const float py = (float)((double)(hvl + vl * (float)y) + vol->origin[1]);
-            const float pz = (float)((double)hvl + vol->origin[2]);
-            // Eigen 4x4 * 4x1 float, coefficient-based lazy product, column-major packets:
-            // ((col0*x + col1*y) + col2*z) + col3*1, separate mul/add roundings (no FMA).
-            float pc[3];
-            for (int r = 0; r < 3; ++r)
-                pc[r] = ((E[r][0] * px + E[r][1] * py) + E[r][2] * pz) + E[r][3] * 1.0f;
-            for (int z = 0; z < R; ++z, pc[0] += Es[0][2], pc[1] += Es[1][2], pc[2] += Es[2][2]) {
-                if (pc[2] <= 0) continue;
-                const float u_f = pc[0] * fx / pc[2] + cx + 0.5f;
-                const float v_f = pc[1] * fy / pc[2] + cy + 0.5f;
-                if (!(u_f >= 0.0001f && u_f < safe_w && v_f >= 0.0001f && v_f < safe_h)) continue;
-                const int u = (int)u_f, v = (int)v_f;
-                const float d = depth[(int64_t)v * W + u];
-                if (d <= 0.0f) continue;
-                const float sdf = (d - pc[2]) * mult[(int64_t)v * W + u];
-                if (sdf > -trunc) {
-                    const float tsdf = std::min(1.0f, sdf * trunc_inv);
-                    const int64_t i = vol->idx(x, y, z);
-                    const float w = vol->weight[i];
-                    vol->tsdf[i] = (vol->tsdf[i] * w + tsdf) / (w + 1.0f);
-                    if (vol->color_type == 1) {
-                        const uint8_t* p = rgb8 + ((int64_t)v * W + u) * 3;
-                        double* c = &vol->color[i * 3];
-                        const double wd = (double)w, w1 = (double)(w + 1.0f);
-                        c[0] = (c[0] * wd + (double)p[0]) / w1;
-                        c[1] = (c[1] * wd + (double)p[1]) / w1;
-                        c[2] = (c[2] * wd + (double)p[2]) / w1;
-                    } else if (vol->color_type == 2) {
-                        double* c = &vol->color[i * 3];
-                        const double g = (double)gray[(int64_t)v * W + u];
-                        const double wd = (double)w, w1 = (double)(w + 1.0f);
-                        c[0] = (c[0] * wd + g) / w1; c[1] = c[0]; c[2] = c[0];
-                    }
-                    vol->weight[i] = w + 1.0f;
-                    ++updates;
-                }
-            }
-        }
-    }
+    for (int x = vol->x_begin; x < vol->x_end; ++x) updates += integrate_x(vol, F, x);
     return updates;
 }
 
