@@ -210,6 +210,29 @@ def run_cpu_icp(K, max_dist=0.004):
             "estimate_normals_s": t_n}
 
 
+def run_cpu_scalable(K, n_frames=4):
+    """ScalableTSDFVolume.integrate on the oracle (hash of 16^3 units, OpenMP over the frame's touched units):
+    frames/s on the host cores for the configuration tools/bench_extra.scalable_bench measures on the GPU."""
+    from b200recon import synthetic as syn
+    from oracle import oracle as orc
+    kt = (K["fx"], K["fy"], K["cx"], K["cy"])
+    poses = syn.orbit_poses(64, radius=0.9, elevation_deg=30.0)
+    sv = orc.ScalableTSDFVolume(0.002, 0.01, 1, 16, 4)
+    frames = []
+    for p in poses[:: max(1, len(poses) // n_frames)][:n_frames]:
+        d16, rgb = orc.raycast_scene(p, kt, K["width"], K["height"])
+        frames.append((orc.depth_to_float(d16), rgb, syn.extrinsic_from_pose(p)))
+    sv.integrate(*frames[0][:2], kt, frames[0][2])          # warm-up (page faults of the first units)
+    t0 = time.perf_counter()
+    upd = 0
+    for d, rgb, ext in frames:
+        upd += sv.integrate(d, rgb, kt, ext)
+    dt = time.perf_counter() - t0
+    return {"value": len(frames) / dt, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": "%d frames 640x480, 2 mm voxels, 16^3 units, stride 4 (unbounded hash: %d units touched in the last frame)"
+                      % (len(frames), sv.touched), "voxel_updates_per_s": upd / dt}
+
+
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
@@ -385,6 +408,11 @@ def run_gpu(args):
         icp["pairs_per_s"] = args.icp_pairs / (icp["ms"] * 1e-3)
         icp["distribution"] = "pair p -> GPU p %% %d, no collective" % world
         extra["icp"] = icp
+        if world == 1 and R <= 1024:
+            try:
+                extra["scalable"] = bench_extra.scalable_bench(1024, 64, 0.9)
+            except Exception as e:
+                extra["scalable"] = {"error": str(e)}
 
     out = None
     if rank == 0:
@@ -481,6 +509,8 @@ def main():
                                    "sample": sample, "voxel_updates_per_s": ups}
             if "icp" in out:
                 out["icp"]["cpu_baseline"] = run_cpu_icp(K)
+            if isinstance(out.get("scalable"), dict) and "error" not in out["scalable"]:
+                out["scalable"]["cpu_baseline"] = run_cpu_scalable(K)
         emit(out)
 
 

@@ -102,6 +102,46 @@ def mesh_bench(vol, reps=2):
             "point_cloud_ms": ms_p, "points": int(p[0].shape[0])}
 
 
+def scalable_bench(resolution=1024, n_frames=64, radius=0.9, steps=None):
+    """ScalableTSDFVolume.integrate (row f4): 640x480 frames of the bench orbit into 2 mm voxels, 16^3 units, stride 4,
+    trunc 10 mm, frames resident in HBM.  Reports frames/s, touched units and updates per frame and the algorithmic
+    bandwidth (24 B per voxel update) of the two kernels together."""
+    import torch
+    import b200recon as o3d
+    from b200recon import synthetic as syn, _lib, runtime
+    integ = o3d.pipelines.integration
+    c = runtime.ctx()
+    K = syn.D435_640x480
+    intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], K["fx"], K["fy"], K["cx"], K["cy"])
+    vol = integ.ScalableTSDFVolume(0.002, 0.01, integ.TSDFVolumeColorType.RGB8, 16, 4, resolution=resolution,
+                                   origin=syn.volume_origin(resolution * 0.002))
+    frames = []
+    for p in syn.orbit_poses(n_frames, radius=radius, elevation_deg=30.0):
+        d16, rgb = syn.render_frame(p, K)
+        d = torch.empty((K["height"], K["width"]), dtype=torch.float32, device=d16.device)
+        _lib.check(_lib.load().b2r_depth_to_float(c.handle, runtime.ptr(d16), 1, K["height"], K["width"], 1000.0, 3.0,
+                                                  runtime.ptr(d), c.stream()))
+        frames.append((d, rgb.contiguous(), syn.extrinsic_from_pose(p)))
+    steps = steps or 4 * n_frames
+    for i in range(8):
+        vol.integrate_device(*frames[i % n_frames][:2], intr, frames[i % n_frames][2])
+    vol.reset()
+    vol.count_updates = True
+
+    def run():
+        for i in range(steps):
+            f = frames[i % n_frames]
+            vol.integrate_device(f[0], f[1], intr, f[2])
+    ms, _ = timed(run)
+    upd = vol.updates()
+    touched = vol.units_touched_last_frame()
+    return {"frames_per_s": steps / (ms * 1e-3), "ms_per_frame": ms / steps, "steps": steps, "resolution": resolution,
+            "voxel_mm": 2.0, "unit": 16, "stride": 4, "updates_per_frame": upd / steps,
+            "units_touched_last_frame": touched, "units_opened": vol.units_opened(), "units_clipped": vol.units_clipped(),
+            "alg_GBps": upd / steps * 24 / (ms / steps * 1e-3) / 1e9,
+            "visited_voxels_per_frame": touched * 4096}
+
+
 def preprocess_bench():
     import b200recon as o3d
     clouds, _ = make_clouds(2, with_normals=False)
@@ -139,6 +179,8 @@ def main():
         d16, rgb = syn.render_frame(p, K)
         vol.integrate_host(d16.cpu().numpy(), rgb.cpu().numpy(), intr, syn.extrinsic_from_pose(p))
     out["mesh_%d" % args.res] = mesh_bench(vol)
+    del vol
+    out["scalable"] = scalable_bench(1024 if args.res >= 1024 else 512, args.frames, 0.9 if args.res >= 1024 else 0.5)
     out["wall_s"] = time.time() - t0
     print(json.dumps(out))
 
