@@ -85,6 +85,26 @@ def compute(orc):
     out["cicp_T"] = r["transformation"]
     out["cicp_stats"] = np.array([r["fitness"], r["inlier_rmse"]])
     out["cicp_iters"] = np.array([r["iterations"], r["n_corr"]], np.int64)
+    # --- ScalableTSDFVolume (row f4): 2 frames of 160x120 into 8^3 units of 6 mm voxels, stride 4
+    K2 = hp.small_intrinsic(160, 120)
+    sv = orc.ScalableTSDFVolume(0.006, 0.024, 1, 8, 4)
+    ns = 0
+    for d16, rgb, ext in hp.make_frames(2, K2, radius=0.35, elevation=65.0):
+        ns += sv.integrate(orc.depth_to_float(d16), rgb, hp.kt(K2), ext)
+    keys = sv.unit_keys()
+    order = np.lexsort((keys[:, 2], keys[:, 1], keys[:, 0]))
+    keys = keys[order]
+    out["scal_updates_units"] = np.array([ns, len(keys), sv.touched], np.int64)
+    out["scal_keys_sha1"] = _digest(keys)
+    out["scal_tsdf_sha1"] = _digest(np.stack([sv.unit_arrays(k)[0] for k in keys]))
+    out["scal_weight_sha1"] = _digest(np.stack([sv.unit_arrays(k)[1] for k in keys]))
+    out["scal_color_sha1"] = _digest(np.stack([sv.unit_arrays(k)[2] for k in keys]))
+    Vs, Ts, _ = sv.extract_triangle_mesh()
+    Ps, Ns, _ = sv.extract_point_cloud()
+    out["scal_counts"] = np.array([len(Vs), len(Ts), len(Ps)], np.int64)
+    out["scal_vertex_sum"] = Vs.sum(0)
+    out["scal_point_sum"] = Ps.sum(0)
+    out["scal_normal_sum"] = Ns.sum(0)
     return out
 
 

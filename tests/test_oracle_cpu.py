@@ -217,7 +217,7 @@ def test_golden_vectors(orc):
     for k in g.files:
         a, b = g[k], cur[k]
         assert a.shape == b.shape and a.dtype == b.dtype, k
-        if a.dtype.kind == "f" and k.startswith(("icp_", "cicp_", "normals_", "grad_", "outlier_stats")):   # OpenMP / libm last bits
+        if a.dtype.kind == "f" and k.startswith(("icp_", "cicp_", "normals_", "grad_", "outlier_stats", "scal_vertex_sum", "scal_point_sum", "scal_normal_sum")):   # OpenMP / libm last bits
             assert np.allclose(a, b, rtol=0, atol=1e-12), k
         else:
             assert np.array_equal(a, b), k
