@@ -58,6 +58,9 @@ struct Scratch {
 
 // Everything one frame needs between its preparation and its items kernel.  Two slots alternate so that
 // frame i+1 is prepared and planned on the caller's stream while frame i still streams on the side stream.
+#ifndef B2R_FRAME_SLOTS
+#define B2R_FRAME_SLOTS 2   // 3 measured no gain: the plan kernel needs free registers beside the persistent kernel, not more slack
+#endif
 struct b2r_frame_slot {
     b2r::Scratch dm, rgba, mip;      // prepared frame: {depth, multiplier} pairs, colour words, max-depth pyramid
     b2r::Scratch hdr, rec, counters; // work items of the frame and their two counters
@@ -71,7 +74,7 @@ struct b2r_ctx {
     int64_t launches = 0;
     // frame staging (prepared frame: {depth_m, multiplier} float2 + packed RGBA)
     b2r::Scratch frame_raw_depth, frame_raw_color, frame_f32;
-    b2r_frame_slot fslot[2];
+    b2r_frame_slot fslot[B2R_FRAME_SLOTS];
     int cur_slot = 0;
     cudaStream_t side = nullptr;     // items kernels run here (B2R_ASYNC=0: on the caller's stream)
     bool async_items = true;
