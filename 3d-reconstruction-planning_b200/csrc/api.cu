@@ -44,9 +44,12 @@ int b2r_ctx_create(int device, b2r_ctx** out) {
         c->async_items = !(e2 && e2[0] == '0');
     }
     B2R_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    B2R_CUDA(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
     for (auto& f : c->fslot) {
         B2R_CUDA(cudaEventCreateWithFlags(&f.ev_plan, cudaEventDisableTiming));
         B2R_CUDA(cudaEventCreateWithFlags(&f.ev_items, cudaEventDisableTiming));
+        B2R_CUDA(cudaEventCreateWithFlags(&f.ev_h2d, cudaEventDisableTiming));
+        B2R_CUDA(cudaEventCreateWithFlags(&f.ev_prep, cudaEventDisableTiming));
     }
     c->pinned_bytes = 1 << 16;
     B2R_CUDA(cudaMallocHost(&c->pinned, c->pinned_bytes));
@@ -58,13 +61,17 @@ int b2r_ctx_destroy(b2r_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
     if (c->side) cudaStreamSynchronize(c->side);
+    if (c->copy) cudaStreamSynchronize(c->copy);
     for (auto& f : c->fslot) {
-        b2r::Scratch* fs[] = {&f.dm, &f.rgba, &f.mip, &f.hdr, &f.rec, &f.counters};
+        b2r::Scratch* fs[] = {&f.dm, &f.rgba, &f.mip, &f.hdr, &f.rec, &f.counters, &f.raw_depth, &f.raw_color};
         for (auto* s : fs) s->release();
         if (f.ev_plan) cudaEventDestroy(f.ev_plan);
         if (f.ev_items) cudaEventDestroy(f.ev_items);
+        if (f.ev_h2d) cudaEventDestroy(f.ev_h2d);
+        if (f.ev_prep) cudaEventDestroy(f.ev_prep);
     }
     if (c->side) cudaStreamDestroy(c->side);
+    if (c->copy) cudaStreamDestroy(c->copy);
     b2r::Scratch* all[] = {&c->frame_raw_depth, &c->frame_raw_color, &c->frame_f32,
                            &c->small, &c->scan_a, &c->scan_b, &c->mc_code, &c->mc_flags, &c->mc_block_counts,
                            &c->mc_vert_id, &c->pc_block_counts, &c->icp_a, &c->icp_b, &c->icp_c, &c->icp_d,

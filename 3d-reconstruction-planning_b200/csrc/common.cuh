@@ -66,6 +66,11 @@ struct b2r_frame_slot {
     b2r::Scratch hdr, rec, counters; // work items of the frame and their two counters
     cudaEvent_t ev_plan = nullptr, ev_items = nullptr;
     bool busy = false;               // ev_items has been recorded
+    // host frames (b2r_integrate_host): raw depth/colour land here from the context's copy stream, so the H2D copy of
+    // frame i+1 runs while the caller's stream still prepares / plans frame i
+    b2r::Scratch raw_depth, raw_color;
+    cudaEvent_t ev_h2d = nullptr, ev_prep = nullptr;
+    bool prep_recorded = false;
 };
 
 struct b2r_ctx {
@@ -77,6 +82,7 @@ struct b2r_ctx {
     b2r_frame_slot fslot[B2R_FRAME_SLOTS];
     int cur_slot = 0;
     cudaStream_t side = nullptr;     // items kernels run here (B2R_ASYNC=0: on the caller's stream)
+    cudaStream_t copy = nullptr;     // H2D copies of b2r_integrate_host
     bool async_items = true;
     cudaEvent_t last_items = nullptr;   // completion of the newest items kernel on the side stream
     b2r::Scratch small;       // counters, per-frame scalars (zero-initialised on creation)

@@ -330,7 +330,7 @@ def run_gpu(args):
 
     def step_e2e(i):
         # pinned HOST frame -> H2D + conversion + plan + streaming kernel; the step's result (running update
-        # count, 8 bytes) is copied device -> pinned host by the library right behind the kernel
+        # count, 8 bytes) is written device -> pinned host by the streaming kernel's last warp
         k = i % nf
         vol.integrate_host(d16_h[k], rgb_h[k], intr, exts[k])
 
@@ -382,9 +382,16 @@ def run_gpu(args):
     # voxel updates of exactly these steps: the same sequence replayed with the counting kernel variant (the
     # count is a deterministic function of the frame sequence since reset)
     vol.count_updates = True
-    _, upd, _ = timed(step_dev, args.steps, args.warmup)
+    c_ms, upd, _ = timed(step_dev, args.steps, args.warmup)
     upd_k_local = timed.local_updates
     e_ms, e_upd, _ = timed(step_e2e, args.steps, args.warmup)
+    if os.environ.get("B2R_BENCH_DIAG"):        # where the e2e step spends its extra time (not part of the JSON contract)
+        vol.count_updates = False
+        n_ms, _, _ = timed(step_e2e, args.steps, args.warmup)
+        vol.count_updates = True
+        timed(step_e2e, 8, 0)
+        sys.stderr.write("diag ms/step: resident %.4f  resident+count %.4f  e2e %.4f  e2e without count %.4f\n"
+                         % (ms / args.steps, c_ms / args.steps, e_ms / args.steps, n_ms / args.steps))
     clocks = sampler.stop() if rank == 0 else None
     mirror = ctx.updates_mirror()
     assert mirror == vol.updates(), "host mirror of the step result disagrees with the device counter"

@@ -73,8 +73,9 @@ int b2r_ctx_launch_count(b2r_ctx* ctx, int64_t* out);
 int b2r_ctx_join(b2r_ctx* ctx, void* stream);
 int b2r_ctx_sync(b2r_ctx* ctx, void* stream); /* join + blocking */
 /* Host mirror of the update counter passed to the most recent b2r_integrate* call as d_updates: the library
- * copies it (8 bytes, device -> pinned host) right behind each frame's streaming kernel.  Not blocking: valid
- * for a frame once that frame has completed (b2r_ctx_sync). */
+ * writes it (8 bytes, device -> mapped pinned host memory, by the last warp of each frame's streaming kernel:
+ * no copy-engine operation between consecutive kernels).  Not blocking: valid for a frame once that frame has
+ * completed (b2r_ctx_sync). */
 int b2r_ctx_updates_mirror(b2r_ctx* ctx, unsigned long long* out);
 /* Per-kernel timing of the dominant kernel (tsdf_integrate) with CUDA events recorded on the launching
  * stream around each launch: enable=1 starts (and clears) collection, enable=0 stops it.
