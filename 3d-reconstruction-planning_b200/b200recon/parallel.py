@@ -78,6 +78,37 @@ def rebalance_slab_ranges(ranges, plane_work, times, min_planes=4):
     return balanced_slab_ranges(cost, len(ranges), min_planes)
 
 
+def agree_plane_work(plane_work, device=None, group=None):
+    """A per-plane cost profile that was MEASURED (profile_plane_cost: kernel timings) differs from rank to rank.
+    Slab boundaries cut from per-rank numbers would not tile the cube, so the ranks agree on the mean profile first
+    (one all_reduce; it also averages the timing noise).  Without a process group: returned unchanged."""
+    rank, world = world_info(group)
+    w = np.asarray(plane_work, np.float64)
+    if world == 1:
+        return w
+    import torch
+    t = torch.as_tensor(w.copy(), device=device if device is not None else "cpu")
+    _dist().all_reduce(t, group=group)
+    return (t / world).cpu().numpy()
+
+
+def check_same_ranges(ranges, resolution, device=None, group=None):
+    """Raises unless `ranges` tiles [0, resolution) and every rank of the group holds the same list."""
+    rank, world = world_info(group)
+    b = [int(a) for a, _ in ranges] + [int(ranges[-1][1])]
+    if b[0] != 0 or b[-1] != int(resolution) or any(int(ranges[i][1]) != int(ranges[i + 1][0]) for i in range(len(ranges) - 1)) \
+            or any(b[i] > b[i + 1] for i in range(len(b) - 1)):
+        raise RuntimeError("slab ranges %r do not tile [0, %d)" % (ranges, resolution))
+    if world == 1:
+        return
+    import torch
+    mine = torch.tensor(b, dtype=torch.int64, device=device if device is not None else "cpu")
+    allb = [torch.zeros_like(mine) for _ in range(world)]
+    _dist().all_gather(allb, mine, group=group)
+    if not all(torch.equal(mine, o) for o in allb):
+        raise RuntimeError("slab boundaries differ between ranks: %r" % [o.tolist() for o in allb])
+
+
 def profile_plane_cost(length, resolution, sdf_trunc, origin, frames, intrinsic, plane_work, chunk=32, color_type=None,
                        device=None):
     """Measured cost profile for `balanced_slab_ranges`: times the streaming kernel of `frames` -- an iterable of

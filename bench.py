@@ -283,9 +283,7 @@ def run_gpu(args):
         work = parallel.profile_plane_cost(L, R, trunc, syn.volume_origin(L), cprobe, intr, work, chunk=32, device=local)
         # the profile is a TIMING, so it differs from rank to rank: every rank must cut the slabs from the same numbers
         # (mean over the ranks -- which also halves the noise), or the slabs would not tile the cube
-        wt = torch.as_tensor(np.asarray(work, np.float64), device=dev)
-        dist.all_reduce(wt)
-        work = (wt / world).cpu().numpy()
+        work = parallel.agree_plane_work(work, device=dev)
         ranges = parallel.balanced_slab_ranges(work, world)
         # one feedback step (the kernel times repeat to about +-5 %, more steps chase noise): time the streaming kernel of every rank on its slab over 12 frames, rescale the work
         # estimate of each slab to its measured time, cut again (setup, outside the timed region; one all_gather of a float)
@@ -310,11 +308,7 @@ def run_gpu(args):
     else:
         ranges = parallel.slab_ranges(R, world)
     if world > 1:      # all ranks must hold the same tiling of [0, R)
-        mine = torch.tensor([a for a, _ in ranges] + [ranges[-1][1]], dtype=torch.int64, device=dev)
-        allb = [torch.zeros_like(mine) for _ in range(world)]
-        dist.all_gather(allb, mine)
-        assert all(torch.equal(mine, o) for o in allb), "slab boundaries differ between ranks"
-        assert ranges[0][0] == 0 and ranges[-1][1] == R and all(ranges[i][1] == ranges[i + 1][0] for i in range(world - 1))
+        parallel.check_same_ranges(ranges, R, device=dev)
     zb, ze = ranges[rank]
     if args.emulate_rank:      # tuning aid: one rank's slab of an N-way split on a single GPU (not a bench line)
         r_, n_ = [int(v) for v in args.emulate_rank.split("/")]

@@ -148,3 +148,54 @@ def test_rebalance_slab_ranges_equalises_measured_time():
     times = np.array([true_cost[a:b].sum() for a, b in rg])
     assert times.max() / times.mean() < 1.12, times
     assert rg[0][0] == 0 and rg[-1][1] == R and all(rg[i][1] == rg[i + 1][0] for i in range(3))
+
+
+def _agree_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        R = 64
+        base = np.zeros(R)
+        base[10:30] = np.linspace(1.0, 3.0, 20)
+        noisy = base * (1.0 + 0.2 * (rank + 1))          # every rank "measures" a different profile
+        local = parallel.balanced_slab_ranges(noisy + 1e-3 * rank * np.arange(R), world)
+        agreed = parallel.agree_plane_work(noisy)
+        ranges = parallel.balanced_slab_ranges(agreed, world)
+        ok = True
+        parallel.check_same_ranges(ranges, R)                            # passes: same numbers everywhere
+        want = base * (1.0 + 0.2 * (sum(range(1, world + 1)) / world))
+        ok &= bool(np.allclose(agreed, want))
+        # a per-rank list that differs is caught on every rank
+        bad = [(0, 20 + rank), (20 + rank, R)] if world == 2 else [(0, 20 + rank), (20 + rank, 40), (40, R)]
+        try:
+            parallel.check_same_ranges(bad, R)
+            ok = False
+        except RuntimeError:
+            pass
+        q.put((rank, bool(ok), local))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_ranks_agree_on_measured_profile_gloo(world):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_agree_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok, _ in res)
+
+
+def test_check_same_ranges_tiling_without_group():
+    parallel.check_same_ranges([(0, 10), (10, 64)], 64)
+    for bad in ([(0, 10), (11, 64)], [(1, 10), (10, 64)], [(0, 10), (10, 63)]):
+        with pytest.raises(RuntimeError):
+            parallel.check_same_ranges(bad, 64)
+    assert np.array_equal(parallel.agree_plane_work([1.0, 2.0]), [1.0, 2.0])
