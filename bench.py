@@ -131,6 +131,15 @@ def orbit(workload):
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle on the host cores (cpu_baseline and --impl reference)
 # ------------------------------------------------------------------------------------------------
+def cpu_threads():
+    """All host cores for the oracle's OpenMP loops, whatever OMP_NUM_THREADS the launcher exported (torchrun sets it
+    to 1 for its workers); returns the team size actually in force -- the `cores` the JSON reports."""
+    from oracle import oracle as orc
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    orc.set_num_threads(n)
+    return orc.max_threads()
+
+
 def cpu_frames(workload, n, K):
     from b200recon import synthetic as syn
     from oracle import oracle as orc
@@ -164,6 +173,7 @@ def cpu_volume(workload):
 def run_cpu(workload, steps, warmup, K, budget_s=25.0):
     """frames/s of the oracle; each step = one frame on the sampled x-range, scaled linearly to R."""
     kt = (K["fx"], K["fy"], K["cx"], K["cy"])
+    cpu_threads()
     vol, scale, xr = cpu_volume(workload)
     frames = cpu_frames(workload, max(1, min(8, steps)), K)
     for i in range(max(1, warmup)):
@@ -190,6 +200,7 @@ def run_cpu_icp(K, max_dist=0.004):
     from b200recon import synthetic as syn
     from oracle import oracle as orc
     kt = (K["fx"], K["fy"], K["cx"], K["cy"])
+    cpu_threads()
     poses = syn.orbit_poses(64, radius=0.5, elevation_deg=30.0)[:2]
     clouds = []
     for p in poses:
@@ -205,7 +216,7 @@ def run_cpu_icp(K, max_dist=0.004):
     t0 = time.perf_counter()
     r = orc.registration_icp(src, clouds[1], Nn, max_dist, np.eye(4), 1, 1e-6, 1e-6, 30)
     dt = time.perf_counter() - t0
-    return {"value": 1.0 / dt, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port", "sample": "1 pair of config 4 "
+    return {"value": 1.0 / dt, "unit": "pairs/s", "cores": cpu_threads(), "kind": "port", "sample": "1 pair of config 4 "
             "(2 x %d points, point-to-plane, r = %g m)" % (len(src), max_dist), "iterations": r["iterations"],
             "estimate_normals_s": t_n}
 
@@ -216,6 +227,7 @@ def run_cpu_scalable(K, n_frames=4):
     from b200recon import synthetic as syn
     from oracle import oracle as orc
     kt = (K["fx"], K["fy"], K["cx"], K["cy"])
+    cpu_threads()
     poses = syn.orbit_poses(64, radius=0.9, elevation_deg=30.0)
     sv = orc.ScalableTSDFVolume(0.002, 0.01, 1, 16, 4)
     frames = []
@@ -228,7 +240,7 @@ def run_cpu_scalable(K, n_frames=4):
     for d, rgb, ext in frames:
         upd += sv.integrate(d, rgb, kt, ext)
     dt = time.perf_counter() - t0
-    return {"value": len(frames) / dt, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+    return {"value": len(frames) / dt, "unit": "frames/s", "cores": cpu_threads(), "kind": "port",
             "sample": "%d frames 640x480, 2 mm voxels, 16^3 units, stride 4 (unbounded hash: %d units touched in the last frame)"
                       % (len(frames), sv.touched), "voxel_updates_per_s": upd / dt}
 
@@ -499,7 +511,7 @@ def main():
         if rank != 0:
             return
         fps, ups, n, sample, dt = run_cpu(args.workload, args.steps, args.warmup, K, budget_s=120.0)
-        cores = os.cpu_count()
+        cores = cpu_threads()
         R = WORKLOADS[args.workload][0]
         emit(({
             "impl": "reference", "metric": "TSDF integration frames/s (%dx%d RGB-D into dense TSDF+colour volume)" % (K["width"], K["height"]),
@@ -517,7 +529,7 @@ def main():
     if out is not None:
         if not args.no_cpu_baseline and args.gpus == 1:
             fps, ups, n, sample, dt = run_cpu(args.workload, 8, 1, K, budget_s=25.0)
-            out["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+            out["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cpu_threads(), "kind": "port",
                                    "sample": sample, "voxel_updates_per_s": ups}
             if "icp" in out:
                 out["icp"]["cpu_baseline"] = run_cpu_icp(K)

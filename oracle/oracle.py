@@ -66,6 +66,8 @@ def lib():
                       ("orc_scalable_normals", c_dp), ("orc_scalable_triangles", C.POINTER(C.c_int32))):
             getattr(L, n).restype = rt
             getattr(L, n).argtypes = [C.c_void_p]
+        L.orc_set_num_threads.argtypes = [C.c_int]
+        L.orc_max_threads.restype = C.c_int
         L.orc_depth_to_float.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_void_p]
         L.orc_distance_multiplier.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_void_p]
         L.orc_backproject.restype = C.c_int64
@@ -99,6 +101,15 @@ def _dp(a):
 
 def _vp(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def set_num_threads(n):
+    """OpenMP team size for the oracle's parallel loops (torchrun exports OMP_NUM_THREADS=1 to its workers)."""
+    lib().orc_set_num_threads(int(n))
+
+
+def max_threads():
+    return int(lib().orc_max_threads())
 
 
 # ---------------------------------------------------------------------------------- images

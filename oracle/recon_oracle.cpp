@@ -16,6 +16,8 @@
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
 // may load this library.  Build: see oracle/Makefile (-O3 -fopenmp -ffp-contract=off, generic
 // x86-64: float32 results must not depend on FMA contraction).
+#include <omp.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -27,6 +29,11 @@
 #include "recon_internal.h"
 
 extern "C" {
+
+// OpenMP team size of the oracle (torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU legs of bench.py
+// ask for all host cores explicitly and report what they got).
+void orc_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int orc_max_threads(void) { return omp_get_max_threads(); }
 
 // ------------------------------------------------------------------------------------------
 // A.1  Image::ConvertDepthToFloatImage(depth_scale, depth_trunc)
