@@ -66,6 +66,8 @@ SIGNATURES = {
     "b2r_integrate": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, C.POINTER(Intrinsic), c_dp, c_vp, c_vp]),
     "b2r_integrate_host": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, C.c_int, c_vp, C.POINTER(Intrinsic), c_dp,
                                      C.c_double, C.c_double, c_vp, c_vp]),
+    "b2r_integrate_host_staged": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, C.c_int, c_vp, C.POINTER(Intrinsic), c_dp,
+                                            C.c_double, C.c_double, c_vp, c_vp]),
     "b2r_integrate_units": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, C.POINTER(Intrinsic), c_dp, c_dp, C.c_int, C.c_int,
                                       C.POINTER(C.c_int32), c_vp, C.c_int32, c_vp, c_vp, c_vp, c_vp]),
     "b2r_selftest_div": (C.c_int, [c_vp, C.c_int64, C.c_uint32, c_i64p, c_vp]),

@@ -65,12 +65,19 @@ _DEPTH_DTYPE = {np.dtype(np.uint8): 0, np.dtype(np.uint16): 1, np.dtype(np.float
 
 
 class RGBDImage:
-    """Open3D geometry.RGBDImage (color + float32-metres depth)."""
+    """Open3D geometry.RGBDImage (color + float32-metres depth).
+
+    `create_from_color_and_depth` is lazy: it validates, keeps the caller's host buffers and the conversion constants,
+    and the float32-metres depth image is produced on the device by whoever needs it first --
+    `PointCloud.create_from_rgbd_image`, `np.asarray(rgbd.depth)`, or never: `UniformTSDFVolume.integrate` hands the
+    raw frame to `b2r_integrate_host_staged`, whose frame-preparation kernel does Open3D's conversion on the fly
+    (one H2D copy of 5 B/pixel instead of a conversion launch + 4 B/pixel float image per frame)."""
 
     def __init__(self):
         self.color = Image()
         self.depth = Image()
         self._depth_dev = None  # float32 metres on device
+        self._raw = None        # (raw depth ndarray, depth_scale, depth_trunc) while the depth is still unconverted
 
     @staticmethod
     def create_from_color_and_depth(color, depth, depth_scale=1000.0, depth_trunc=3.0, convert_rgb_to_intensity=True):
@@ -81,15 +88,6 @@ class RGBDImage:
             raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
         if depth.num_of_channels != 1:
             raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
-        c = runtime.ctx()
-        t = runtime.torch()
-        H, W = depth.height, depth.width
-        out = t.empty((H, W), dtype=t.float32, device=c.tdev)
-        if H * W:
-            d_in = depth.device_tensor()
-            _lib.check(_lib.load().b2r_depth_to_float(c.handle, runtime.ptr(d_in), _DEPTH_DTYPE[depth._a.dtype], H, W,
-                                                      float(depth_scale), float(depth_trunc), runtime.ptr(out),
-                                                      c.stream()))
         rgbd = RGBDImage()
         if convert_rgb_to_intensity:
             a = color._a
@@ -103,9 +101,25 @@ class RGBDImage:
             rgbd.color = Image(g.astype(np.float32))
         else:
             rgbd.color = color
-        rgbd._depth_dev = out
-        rgbd.depth = _LazyDepthImage(out)
+        rgbd._raw = (depth._a if depth._a.ndim == 2 else depth._a.reshape(depth.height, depth.width),
+                     float(depth_scale), float(depth_trunc))
+        rgbd.depth = _LazyDepthImage(rgbd)
         return rgbd
+
+    def _depth_device(self):
+        """float32 metres [H,W] on the device (Image.ConvertDepthToFloatImage, b2r_depth_to_float), made on first use."""
+        if self._depth_dev is None and self._raw is not None:
+            raw, scale, trunc = self._raw
+            c = runtime.ctx()
+            t = runtime.torch()
+            H, W = raw.shape
+            out = t.empty((H, W), dtype=t.float32, device=c.tdev)
+            if H * W:
+                d_in = runtime.to_device(raw)
+                _lib.check(_lib.load().b2r_depth_to_float(c.handle, runtime.ptr(d_in), _DEPTH_DTYPE[raw.dtype], H, W,
+                                                          scale, trunc, runtime.ptr(out), c.stream()))
+            self._depth_dev = out
+        return self._depth_dev
 
     def __repr__(self):
         return "RGBDImage of size \nColor image : %dx%d, with %d channels.\nDepth image : %dx%d, with %d channels." % (
@@ -114,11 +128,16 @@ class RGBDImage:
 
 
 class _LazyDepthImage(Image):
-    """Depth image that stays on the device until somebody asks for the numpy buffer."""
+    """The RGBD's depth image: float32 metres, converted on the device on first use, copied to the host only when
+    somebody asks for the numpy buffer."""
 
-    def __init__(self, dev):
-        self._dev = dev
+    def __init__(self, rgbd):
+        self._rgbd = rgbd
         self._host = None
+
+    @property
+    def _dev(self):
+        return self._rgbd._depth_device()
 
     @property
     def _a(self):
@@ -128,11 +147,11 @@ class _LazyDepthImage(Image):
 
     @property
     def width(self):
-        return int(self._dev.shape[1])
+        return int(self._rgbd._raw[0].shape[1])
 
     @property
     def height(self):
-        return int(self._dev.shape[0])
+        return int(self._rgbd._raw[0].shape[0])
 
     @property
     def num_of_channels(self):
@@ -147,6 +166,8 @@ class _LazyDepthImage(Image):
 
 
 def _depth_f32_device(rgbd):
+    if isinstance(rgbd, RGBDImage) and rgbd._raw is not None:
+        return rgbd._depth_device()
     if getattr(rgbd, "_depth_dev", None) is not None:
         return rgbd._depth_dev
     d = rgbd.depth
@@ -317,6 +338,8 @@ class PointCloud:
     def __iadd__(self, other):
         """stitcher.py:136 -- Open3D keeps colors/normals only when both clouds have them."""
         t = runtime.torch()
+        if len(other._p) == 0:      # Open3D's operator+= returns early: colours / normals of `self` survive
+            return self
         n0 = len(self._p)
         keep_c = (n0 == 0 or self.has_colors()) and other.has_colors()
         keep_n = (n0 == 0 or self.has_normals()) and other.has_normals()

@@ -8,6 +8,7 @@
 """
 import json
 import os
+import re
 
 import numpy as np
 
@@ -176,3 +177,81 @@ def read_frames_realsense(data_folder):
     if os.path.exists(mp):
         meta = json.load(open(mp))
     return colors, depths, meta
+
+
+def read_frames_bullet_camera(folder_path, rgb_foldername="rgb", depth_foldername="depth", modulus=2):
+    """The simulator's on-disk layout (bullet_camera.py:71-85): `<folder>/rgb/rgb_%04d.png` (BGR as cv2 writes it) and
+    `<folder>/depth/depth_%04d.png` (the GL depth buffer x 255 as **uint8** -- Open3D then reads it as v/255/1000 m,
+    SURVEY A.1: garbage in, but defined behaviour).  Same result as RGBDStitcher.load_dataset_two_folders
+    (stitcher.py:208-233): sorted file order, cv2.imread / IMREAD_UNCHANGED, trailing frames dropped so that the count
+    is a multiple of `modulus` (optimization_modulus = 2, stitcher.py:19,228-231)."""
+    import cv2
+    colors, depths = [], []
+    rgb_folder = os.path.join(folder_path, rgb_foldername)
+    for fn in sorted(os.listdir(rgb_folder)):
+        colors.append(cv2.imread(os.path.join(rgb_folder, fn)))
+    depth_folder = os.path.join(folder_path, depth_foldername)
+    for fn in sorted(os.listdir(depth_folder)):
+        depths.append(cv2.imread(os.path.join(depth_folder, fn), cv2.IMREAD_UNCHANGED))
+    if modulus > 1 and len(colors) % modulus:
+        for _ in range(len(colors) % modulus):
+            colors.pop()
+            depths.pop()
+    return colors, depths
+
+
+def pose_from_position_quaternion(position, quat_xyzw):
+    """4x4 pose from a position and an (x, y, z, w) quaternion -- scipy's Rotation.from_quat order, which is what
+    Expansion-GRR/grr/utils.py:101-105 (matrix_to_quat) writes into wtraj.txt."""
+    x, y, z, w = [float(v) for v in quat_xyzw]
+    n = np.sqrt(x * x + y * y + z * z + w * w)
+    if n == 0.0:
+        raise ValueError("zero quaternion")
+    x, y, z, w = x / n, y / n, z / n, w / n
+    T = np.eye(4)
+    T[:3, :3] = [[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                 [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                 [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]]
+    T[:3, 3] = [float(v) for v in position]
+    return T
+
+
+_CALL = re.compile(r"[A-Za-z_][A-Za-z_0-9.]*\(")
+_NUM = re.compile(r"[-+]?(?:\d+\.?\d*|\.\d+)(?:[eE][-+]?\d+)?")
+
+
+def read_trajectory(filename):
+    """Pose source of the simulator run: `wtraj.txt` (main.py:156-165) / `wtraj_input.txt` (main.py:138-140), one
+    waypoint per line as Python reprs -- `t,[array([x, y, z]), array([qx, qy, qz, qw])]` resp.
+    `[x, y, z],[qx, qy, qz, qw]` (no time stamp).  Returns (times float64 [N] or None, poses float64 [N,4,4]); the
+    poses are the end-effector / camera-link frames in the robot's world, usable as ICP `init` after expressing them
+    relative to the first frame (`relative_poses`)."""
+    times, poses = [], []
+    with open(filename) as f:
+        for line in f:
+            # drop the constructor names of the reprs ("array(", numpy 2's "np.float64(") before picking the numbers
+            v = [float(x) for x in _NUM.findall(_CALL.sub("(", line))]
+            if not v:
+                continue
+            if len(v) == 8:
+                times.append(v[0])
+                v = v[1:]
+            if len(v) != 7:
+                raise ValueError("read_trajectory: cannot parse %r" % line[:80])
+            poses.append(pose_from_position_quaternion(v[:3], v[3:]))
+    return (np.asarray(times) if len(times) == len(poses) and times else None), np.asarray(poses).reshape(-1, 4, 4)
+
+
+def relative_poses(poses, reference=0):
+    """poses[i] expressed in the frame of poses[reference]: inv(poses[reference]) @ poses[i]."""
+    P = np.asarray(poses, np.float64).reshape(-1, 4, 4)
+    inv0 = np.linalg.inv(P[reference])
+    return np.stack([inv0 @ p for p in P])
+
+
+def select_waypoints(n_waypoints, n_images):
+    """Indices of the waypoints at which main.py:213-232 takes its `img_total` pictures: image k is taken as soon as
+    1 + floor((img_total - 1) / maneuver_time * t) exceeds the count, i.e. at trajectory fraction k / (img_total - 1)."""
+    if n_images <= 1:
+        return [0] * max(n_images, 0)
+    return [int(round(k * (n_waypoints - 1) / (n_images - 1))) for k in range(n_images)]

@@ -279,13 +279,15 @@ class SlabVolume:
     The mesh is the single-volume mesh: same vertex and triangle sets (vertex ids are global)."""
 
     def __init__(self, length, resolution, sdf_trunc, color_type=None, origin=(0.0, 0.0, 0.0), group=None, device=None,
-                 z_ranges=None):
+                 z_ranges=None, local=None):
         """z_ranges: optional [(z_begin, z_end)] per rank (contiguous, covering [0, resolution)), e.g. from
-        `balanced_slab_ranges`; default = equal plane counts."""
+        `balanced_slab_ranges`; default = equal plane counts.  local: this rank's slab if it already exists (a
+        `UniformTSDFVolume(z_range=z_ranges[rank])`), else it is created here."""
         from .pipelines import integration
         self.group = group
         self.rank, self.world = world_info(group)
         self.resolution = int(resolution)
+        self.timings = {}
         ct = integration.TSDFVolumeColorType.RGB8 if color_type is None else color_type
         if z_ranges is None:
             z_ranges = slab_ranges(resolution, self.world)
@@ -297,9 +299,31 @@ class SlabVolume:
         if self.world > 1 and (self.z_end - self.z_begin) < max(_lib.PAD_LO, _lib.PAD_HI):
             raise RuntimeError("SlabVolume: %d planes over %d ranks leaves slabs thinner than the halo" %
                                (self.resolution, self.world))
-        self.local = integration.UniformTSDFVolume(length, resolution, sdf_trunc, ct, origin,
-                                                   z_range=(self.z_begin, self.z_end), device=device)
+        if local is not None:
+            if (local.z_begin, local.z_end, local.resolution) != (self.z_begin, self.z_end, self.resolution):
+                raise RuntimeError("SlabVolume: `local` is slab [%d,%d) of %d, this rank owns [%d,%d) of %d" % (
+                    local.z_begin, local.z_end, local.resolution, self.z_begin, self.z_end, self.resolution))
+            self.local = local
+        else:
+            self.local = integration.UniformTSDFVolume(length, resolution, sdf_trunc, ct, origin,
+                                                       z_range=(self.z_begin, self.z_end), device=device)
         self._halo_valid = False
+
+    def _timed(self, key, fn):
+        """Runs fn(); when `self.timings` collection is on (`timings["on"]`), brackets it with CUDA events on the
+        current stream + a synchronize and accumulates milliseconds under `key`."""
+        if not self.timings.get("on"):
+            return fn()
+        import torch
+        dev = self.local._ctx.tdev
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(dev)
+        e0.record()
+        out = fn()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        self.timings[key] = self.timings.get(key, 0.0) + e0.elapsed_time(e1)
+        return out
 
     # ---- integration: no collective -------------------------------------------------------------
     def integrate(self, image, intrinsic, extrinsic):
@@ -334,17 +358,23 @@ class SlabVolume:
         from . import geometry
         v = self.local
         dev = v._ctx.tdev
-        self.exchange_halos()
-        nv, nt = v._mesh_count()
-        counts = all_gather_counts([nv, nt], dev, self.group)            # [world, 2]
+        self._timed("halo_ms", self.exchange_halos)
+        nv, nt = self._timed("count_ms", v._mesh_count)
+        counts = self._timed("seam_ms", lambda: all_gather_counts([nv, nt], dev, self.group))   # [world, 2]
         vbase = exclusive_bases(counts[:, 0])
-        V, Cc = v._mesh_vertices(nv, vertex_base=int(vbase[self.rank]))  # fills the slab's vertex-id table
+        # fills the slab's vertex-id table
+        V, Cc = self._timed("emit_ms", lambda: v._mesh_vertices(nv, vertex_base=int(vbase[self.rank])))
         if self.world > 1:
-            self._exchange_seam()
-        T = v._mesh_triangles(nt)
-        Vg = gather_rows(V, counts[:, 0], dst, self.group)
-        Cg = gather_rows(Cc, counts[:, 0], dst, self.group) if Cc is not None else None
-        Tg = gather_rows(T, counts[:, 1], dst, self.group)
+            self._timed("seam_ms", self._exchange_seam)
+        T = self._timed("emit_ms", lambda: v._mesh_triangles(nt))
+
+        def gather():
+            Vg = gather_rows(V, counts[:, 0], dst, self.group)
+            Cg = gather_rows(Cc, counts[:, 0], dst, self.group) if Cc is not None else None
+            Tg = gather_rows(T, counts[:, 1], dst, self.group)
+            return Vg, Cg, Tg
+        Vg, Cg, Tg = self._timed("gather_ms", gather)
+        self.last_counts = counts
         if self.rank != dst:
             return None
         m = geometry.TriangleMesh()
@@ -395,6 +425,182 @@ class SlabVolume:
         if Cg is not None:
             pcd._c.set_dev(Cg)
         return pcd
+
+
+# --------------------------------------------------------------------------------------------------
+# several slabs of one cube in ONE process (one GPU, or the GPUs of one process)
+# --------------------------------------------------------------------------------------------------
+def _raw_i32(ptr, n, tdev):
+    import torch
+    return torch.as_tensor(_RawCuda(ptr, n), device=tdev)
+
+
+class LocalSlabs:
+    """The z-slab decomposition of `SlabVolume` without a process group: every slab is a `UniformTSDFVolume` with its
+    own library context (own scratch, side stream and extraction state) on one device of this process, and the
+    exchange steps -- halo planes, the seam plane of the vertex-id table -- are device-to-device copies instead of
+    NCCL messages.  Same kernels, same C-ABI calls (`vertex_base`, `b2r_mesh_seam_buffers`), same result: the
+    single-volume mesh / point cloud.  Uses: cubes cut into slabs that are extracted one after the other with a
+    bounded scratch footprint, and the seam logic under test on a single GPU (tests/test_slab_seam_gpu.py)."""
+
+    def __init__(self, length, resolution, sdf_trunc, color_type=None, origin=(0.0, 0.0, 0.0), z_ranges=None,
+                 n_slabs=2, device=None):
+        from . import runtime
+        from .pipelines import integration
+        self.resolution = int(resolution)
+        ct = integration.TSDFVolumeColorType.RGB8 if color_type is None else color_type
+        if z_ranges is None:
+            z_ranges = slab_ranges(resolution, n_slabs)
+        z_ranges = [(int(a), int(b)) for a, b in z_ranges]
+        n = len(z_ranges)
+        if (z_ranges[0][0] != 0 or z_ranges[-1][1] != self.resolution or
+                any(z_ranges[i][1] != z_ranges[i + 1][0] for i in range(n - 1))):
+            raise RuntimeError("LocalSlabs: z_ranges must be contiguous slabs covering [0, %d)" % self.resolution)
+        if n > 1 and min(b - a for a, b in z_ranges) < max(_lib.PAD_LO, _lib.PAD_HI):
+            raise RuntimeError("LocalSlabs: a slab is thinner than the halo (%d planes)" % max(_lib.PAD_LO, _lib.PAD_HI))
+        self.z_ranges = z_ranges
+        self.slabs = [integration.UniformTSDFVolume(length, resolution, sdf_trunc, ct, origin, z_range=zr, device=device,
+                                                    context=runtime.new_context(device)) for zr in z_ranges]
+        self._halo_valid = False
+
+    def __len__(self):
+        return len(self.slabs)
+
+    def integrate(self, image, intrinsic, extrinsic):
+        for v in self.slabs:
+            v.integrate(image, intrinsic, extrinsic)
+        self._halo_valid = False
+
+    def integrate_host(self, depth, color, intrinsic, extrinsic, depth_scale=1000.0, depth_trunc=3.0):
+        for v in self.slabs:
+            v.integrate_host(depth, color, intrinsic, extrinsic, depth_scale, depth_trunc)
+        self._halo_valid = False
+
+    def integrate_device(self, depth_f32, color, intrinsic, extrinsic):
+        for v in self.slabs:
+            v.integrate_device(depth_f32, color, intrinsic, extrinsic)
+        self._halo_valid = False
+
+    def reset(self):
+        for v in self.slabs:
+            v.reset()
+        self._halo_valid = False
+
+    def import_arrays(self, tsdf, weight, color=None):
+        for v, (a, b) in zip(self.slabs, self.z_ranges):
+            v.import_arrays(tsdf[:, :, a:b], weight[:, :, a:b], None if color is None else color[:, :, a:b])
+        self._halo_valid = False
+
+    def exchange_halos(self):
+        """Same planes as `halo_plan` moves between ranks: first PAD_HI owned planes of slab k+1 -> top pad of slab k,
+        last PAD_LO owned planes of slab k -> bottom pad of slab k+1."""
+        if self._halo_valid:
+            return
+        lo, hi = _lib.PAD_LO, _lib.PAD_HI
+        for v in self.slabs:
+            v._ctx.join()
+        for k in range(len(self.slabs) - 1):
+            a, b = self.slabs[k], self.slabs[k + 1]
+            na = a.z_end - a.z_begin
+            for ta, tb in ((a._tsdfw, b._tsdfw), (a._color, b._color)):
+                if ta is None:
+                    continue
+                ta[lo + na:lo + na + hi].copy_(tb[lo:lo + hi])
+                tb[0:lo].copy_(ta[lo + na - lo:lo + na])
+        self._halo_valid = True
+
+    def extract_triangle_mesh_device(self):
+        """(vertices, triangles, colors|None) CUDA tensors of the whole cube; vertex ids are global."""
+        import ctypes as C
+        import torch
+        self.exchange_halos()
+        counts = [v._mesh_count() for v in self.slabs]
+        # NOTE: every slab has its own context, so the count state of slab k survives the count of slab k+1
+        bases = exclusive_bases([c[0] for c in counts])
+        Vs, Cs = [], []
+        for v, (nv, _), base in zip(self.slabs, counts, bases):
+            V, Cc = v._mesh_vertices(nv, vertex_base=int(base))
+            Vs.append(V)
+            Cs.append(Cc)
+        lib = _lib.load()
+        bufs = []
+        for v in self.slabs:
+            send, recv, nbytes = C.c_void_p(), C.c_void_p(), C.c_int64(0)
+            _lib.check(lib.b2r_mesh_seam_buffers(v._ctx.handle, C.byref(v._desc), C.byref(send), C.byref(recv),
+                                                 C.byref(nbytes)))
+            bufs.append((send.value, recv.value, nbytes.value // 4))
+        for k in range(len(self.slabs) - 1):      # first owned plane of slab k+1's id table -> pad plane above slab k
+            tdev = self.slabs[k]._ctx.tdev
+            _raw_i32(bufs[k][1], bufs[k][2], tdev).copy_(_raw_i32(bufs[k + 1][0], bufs[k + 1][2], tdev))
+        Ts = [v._mesh_triangles(nt) for v, (_, nt) in zip(self.slabs, counts)]
+        V = torch.cat(Vs)
+        T = torch.cat(Ts)
+        Cc = torch.cat(Cs) if Cs[0] is not None else None
+        return V, T, Cc
+
+    def extract_triangle_mesh(self):
+        from . import geometry
+        V, T, Cc = self.extract_triangle_mesh_device()
+        m = geometry.TriangleMesh()
+        m.vertices = V.cpu().numpy()
+        m.triangles = T.cpu().numpy()
+        if Cc is not None:
+            m.vertex_colors = Cc.cpu().numpy()
+        return m
+
+    def extract_point_cloud(self):
+        import torch
+        from . import geometry
+        self.exchange_halos()
+        parts = [v.extract_point_cloud_device() for v in self.slabs]
+        pcd = geometry.PointCloud()
+        pcd._p.set_dev(torch.cat([p[0] for p in parts]))
+        pcd._n.set_dev(torch.cat([p[1] for p in parts]))
+        if parts[0][2] is not None:
+            pcd._c.set_dev(torch.cat([p[2] for p in parts]))
+        return pcd
+
+
+# --------------------------------------------------------------------------------------------------
+# order-independent mesh digest (to compare the gathered mesh of N slabs with the single-volume mesh)
+# --------------------------------------------------------------------------------------------------
+def _mix64(x):
+    x = x.astype(np.uint64, copy=True)
+    x ^= x >> np.uint64(30)
+    x *= np.uint64(0xBF58476D1CE4E5B9)
+    x ^= x >> np.uint64(27)
+    x *= np.uint64(0x94D049BB133111EB)
+    x ^= x >> np.uint64(31)
+    return x
+
+
+def mesh_checksum(vertices, triangles, quantum):
+    """Digest of a triangle mesh that does not depend on vertex order, triangle order, vertex numbering or on which
+    corner a triangle starts with (its orientation does count): vertices are quantised to `quantum` (metres; e.g.
+    1e-4 voxel, the parity tolerance) and hashed; a triangle is hashed from its corners' vertex hashes rotated so the
+    smallest comes first.  Returns {"vertices": n, "triangles": n, "vertex_sum": hex, "triangle_sum": hex}: equal
+    digests <=> equal quantised vertex sets and equal oriented triangle sets (up to 64-bit hash collisions)."""
+    V = np.asarray(vertices, np.float64).reshape(-1, 3)
+    T = np.asarray(triangles, np.int64).reshape(-1, 3)
+    with np.errstate(over="ignore"):
+        q = np.round(V / float(quantum)).astype(np.int64).view(np.uint64)
+        vh = _mix64(q[:, 0] + _mix64(q[:, 1] + _mix64(q[:, 2])))
+        vsum = int(np.add.reduce(vh, dtype=np.uint64)) if len(vh) else 0
+        tsum = 0
+        if len(T):
+            h = vh[T]
+            # canonical rotation = the lexicographically smallest of the three (ties between equal corner hashes --
+            # degenerate triangles, which Open3D keeps -- are then resolved the same way whatever the start corner)
+            r1, r2 = np.roll(h, -1, axis=1), np.roll(h, -2, axis=1)
+
+            def less(a, b):
+                return (a[:, 0] < b[:, 0]) | ((a[:, 0] == b[:, 0]) & ((a[:, 1] < b[:, 1]) | ((a[:, 1] == b[:, 1]) & (a[:, 2] < b[:, 2]))))
+            best = np.where(less(r1, h)[:, None], r1, h)
+            h = np.where(less(r2, best)[:, None], r2, best)
+            th = _mix64(h[:, 0] + _mix64(h[:, 1] * np.uint64(3) + _mix64(h[:, 2] * np.uint64(5))))
+            tsum = int(np.add.reduce(th, dtype=np.uint64))
+    return {"vertices": int(len(V)), "triangles": int(len(T)), "vertex_sum": "%016x" % vsum,
+            "triangle_sum": "%016x" % tsum}
 
 
 # --------------------------------------------------------------------------------------------------

@@ -1,2 +1,2 @@
-"""`o3d.pipelines` subset: integration (TSDF) and registration (ICP)."""
-from . import integration, registration  # noqa: F401
+"""`o3d.pipelines` subset: integration (TSDF), registration (ICP) and the fused ICP -> integrate -> mesh path."""
+from . import integration, registration, fusion  # noqa: F401

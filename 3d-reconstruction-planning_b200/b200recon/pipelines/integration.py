@@ -28,7 +28,8 @@ class TSDFVolume:
 
 class UniformTSDFVolume(TSDFVolume):
     def __init__(self, length, resolution, sdf_trunc, color_type=TSDFVolumeColorType.RGB8, origin=(0.0, 0.0, 0.0),
-                 z_range=None, device=None):
+                 z_range=None, device=None, context=None):
+        """`z_range` / `device` / `context` are extensions (multi-GPU slabs, several slabs in one process)."""
         self.length = float(length)
         self.resolution = int(resolution)
         self.sdf_trunc = float(sdf_trunc)
@@ -41,7 +42,7 @@ class UniformTSDFVolume(TSDFVolume):
         if not (0 <= zb <= ze <= self.resolution):
             raise RuntimeError("UniformTSDFVolume: bad z_range %r" % (z_range,))
         self.z_begin, self.z_end = zb, ze
-        self._ctx = runtime.ctx(device)
+        self._ctx = context if context is not None else runtime.ctx(device)
         t = runtime.torch()
         R = self.resolution
         planes = (ze - zb) + _lib.PAD_LO + _lib.PAD_HI
@@ -57,8 +58,30 @@ class UniformTSDFVolume(TSDFVolume):
         self.count_updates = False
 
     # ------------------------------------------------------------------ integrate
+    _RAW_FRAME_PATH = True      # integrate() may hand an unconverted RGBDImage to b2r_integrate_host_staged
+
     def integrate(self, image, intrinsic, extrinsic):
-        """Open3D UniformTSDFVolume.integrate(rgbd, intrinsic, extrinsic); extrinsic = world->camera."""
+        """Open3D UniformTSDFVolume.integrate(rgbd, intrinsic, extrinsic); extrinsic = world->camera.
+
+        An RGBDImage fresh from `create_from_color_and_depth` (stitcher.py:38-42) still holds the caller's raw host
+        frame: it goes through `b2r_integrate_host_staged` (pinned staging + one H2D DMA + conversion inside the
+        frame-preparation kernel).  An RGBDImage whose float depth already exists on the device takes
+        `b2r_integrate`."""
+        raw = getattr(image, "_raw", None)
+        if (self._RAW_FRAME_PATH and raw is not None and image._depth_dev is None
+                and self.color_type != TSDFVolumeColorType.Gray32):
+            d, scale, trunc = raw
+            H, W = d.shape
+            if (W, H) != (intrinsic.width, intrinsic.height):
+                raise RuntimeError("[UniformTSDFVolume::Integrate] Unsupported image format.")
+            col = None
+            if self.color_type == TSDFVolumeColorType.RGB8:
+                ci = image.color
+                if ci.num_of_channels != 3 or ci.bytes_per_channel != 1 or (ci.width, ci.height) != (W, H):
+                    raise RuntimeError("[UniformTSDFVolume::Integrate] Unsupported image format.")
+                col = ci._a
+            self._integrate_host_checked(d, col, intrinsic, extrinsic, scale, trunc, staged=True)
+            return
         depth = geometry._depth_f32_device(image)
         H, W = int(depth.shape[0]), int(depth.shape[1])
         if (W, H) != (intrinsic.width, intrinsic.height):
@@ -86,29 +109,101 @@ class UniformTSDFVolume(TSDFVolume):
                                              C.byref(K), ext, upd, c.stream()))
 
     def integrate_host(self, depth, color, intrinsic, extrinsic, depth_scale=1000.0, depth_trunc=3.0):
-        """End-to-end entry: raw HOST frame (numpy or pinned torch CPU tensors: depth uint8/uint16/float32,
-        colour uint8 [H,W,3]) -> H2D copy + depth conversion (stitcher.py:40-41 constants) + integrate."""
-        c = self._ctx
+        """End-to-end entry: raw HOST frame -> H2D copy + depth conversion (stitcher.py:40-41 constants) + integrate.
+        depth: uint8/uint16/float32 [H,W]; colour: uint8 [H,W,3] (RGB8 volumes; ignored by NoColor volumes).
+
+        * numpy arrays (pageable): copied into the library's pinned staging ring first
+          (`b2r_integrate_host_staged`); the arrays may be reused as soon as the call returns.
+        * pinned torch CPU tensors: DMA'd straight from the caller's memory (`b2r_integrate_host`, no host copy).
+          The volume keeps a reference to them until the copy has completed, but the caller must not MODIFY them
+          before then (`vol.updates()`, `ctx.sync()` or any synchronisation of the current stream).
+        Shape, dtype and contiguity are checked against the intrinsic like Open3D's Integrate does
+        ("Unsupported image format")."""
         t = runtime.torch()
-        dt = {t.uint8: 0, t.uint16: 1, t.float32: 2}
-        if isinstance(depth, np.ndarray):
-            depth = t.from_numpy(np.ascontiguousarray(depth))
-        if isinstance(color, np.ndarray):
-            color = t.from_numpy(np.ascontiguousarray(color))
-        if depth.dtype not in dt:
-            raise RuntimeError("[CreateFromColorAndDepth] Unsupported image format.")
+        if self.color_type == TSDFVolumeColorType.Gray32:
+            raise RuntimeError("[UniformTSDFVolume::Integrate] Unsupported image format. (Gray32 volumes take a float "
+                               "colour image through integrate())")
+        pinned = isinstance(depth, t.Tensor)
+        if pinned != (isinstance(color, t.Tensor) or color is None):
+            raise RuntimeError("integrate_host: depth and colour must both be numpy arrays or both torch CPU tensors")
+        if pinned:
+            if depth.is_cuda or (color is not None and color.is_cuda):
+                raise RuntimeError("integrate_host takes HOST frames; use integrate_device for CUDA tensors")
+            if not depth.is_pinned() or (color is not None and self.color_type == TSDFVolumeColorType.RGB8 and not color.is_pinned()):
+                depth = depth.numpy()           # pageable torch tensors: same path as numpy
+                color = None if color is None else color.numpy()
+                pinned = False
+        self._integrate_host_checked(depth, color, intrinsic, extrinsic, depth_scale, depth_trunc, staged=not pinned)
+
+    _HOST_DT_NP = {np.dtype(np.uint8): 0, np.dtype(np.uint16): 1, np.dtype(np.float32): 2}
+
+    def _integrate_host_checked(self, depth, color, intrinsic, extrinsic, depth_scale, depth_trunc, staged):
+        t = runtime.torch()
+        c = self._ctx
+        H, W = int(intrinsic.height), int(intrinsic.width)
+        bad = RuntimeError("[UniformTSDFVolume::Integrate] Unsupported image format.")
+        need_color = self.color_type == TSDFVolumeColorType.RGB8
+        if staged:
+            if not isinstance(depth, np.ndarray) or depth.dtype not in self._HOST_DT_NP or depth.shape not in ((H, W), (H, W, 1)):
+                raise bad
+            depth = np.ascontiguousarray(depth)
+            dcode, dptr = self._HOST_DT_NP[depth.dtype], depth.ctypes.data
+            cptr = 0
+            if need_color:
+                if not isinstance(color, np.ndarray) or color.dtype != np.uint8 or color.shape != (H, W, 3):
+                    raise bad
+                color = np.ascontiguousarray(color)
+                cptr = color.ctypes.data
+            fn = _lib.load().b2r_integrate_host_staged
+        else:
+            dt = {t.uint8: 0, t.uint16: 1, t.float32: 2}
+            if depth.dtype not in dt or tuple(depth.shape) not in ((H, W), (H, W, 1)) or not depth.is_contiguous():
+                raise bad
+            dcode, dptr = dt[depth.dtype], depth.data_ptr()
+            cptr = 0
+            if need_color:
+                if color is None or color.dtype != t.uint8 or tuple(color.shape) != (H, W, 3) or not color.is_contiguous():
+                    raise bad
+                cptr = color.data_ptr()
+            fn = _lib.load().b2r_integrate_host
+            self._hold(depth, color if need_color else None)
         _, ext = runtime.mat16(extrinsic)
         K = intrinsic._c()
         upd = runtime.ptr(self._updates) if self.count_updates else C.c_void_p(0)
-        _lib.check(_lib.load().b2r_integrate_host(c.handle, C.byref(self._desc), C.c_void_p(depth.data_ptr()),
-                                                  dt[depth.dtype], C.c_void_p(0 if color is None else color.data_ptr()),
-                                                  C.byref(K), ext, float(depth_scale), float(depth_trunc), upd,
-                                                  c.stream()))
+        _lib.check(fn(c.handle, C.byref(self._desc), C.c_void_p(dptr), dcode, C.c_void_p(cptr), C.byref(K), ext,
+                      float(depth_scale), float(depth_trunc), upd, c.stream()))
+
+    # Pinned caller frames are read by an asynchronous DMA after integrate_host has returned: keep them alive until an
+    # event recorded on the current stream BEHIND the call (the stream waits for the copy) has completed.  One event
+    # per _HOLD_EVERY frames, not per frame.
+    _HOLD_EVERY = 16
+
+    def _hold(self, *tensors):
+        t = runtime.torch()
+        if not hasattr(self, "_held"):
+            self._held, self._guards = [], []
+        self._held.append(tensors)
+        if len(self._held) >= self._HOLD_EVERY:
+            # the event is recorded at the start of the NEXT call, i.e. behind every frame in `held`
+            ev = t.cuda.Event()
+            ev.record(t.cuda.current_stream(self._ctx.tdev))
+            # (this call's own frame was appended above but its copy is not queued yet: it stays in the new list)
+            self._guards.append((ev, self._held[:-1]))
+            self._held = self._held[-1:]
+            while self._guards and self._guards[0][0].query():
+                self._guards.pop(0)
+
+    def _release_held(self):
+        """after a host-side synchronisation that covers every queued copy"""
+        if hasattr(self, "_held"):
+            self._held, self._guards = [], []
 
     def updates(self):
         """Number of voxel updates counted since the last reset (needs count_updates=True)."""
         self._ctx.join()
-        return int(self._updates.item())
+        n = int(self._updates.item())       # blocks on the current stream, which is ordered after every copy
+        self._release_held()
+        return n
 
     def __del__(self):
         # the volume's tensors go back to torch's allocator: no streaming kernel may still be writing them
@@ -243,6 +338,8 @@ class ScalableTSDFVolume(UniformTSDFVolume):
 
     Differences from Open3D: vertex / point order (memory order instead of hash-iteration order); voxels on the
     outermost layer of the backing cube produce no points (the dense extraction's border rule)."""
+
+    _RAW_FRAME_PATH = False     # the unit kernels take the converted float depth image (b2r_integrate_units)
 
     def __init__(self, voxel_length, sdf_trunc, color_type=TSDFVolumeColorType.RGB8, volume_unit_resolution=16,
                  depth_sampling_stride=4, *, resolution=512, origin=None, unit_offset=None, device=None):

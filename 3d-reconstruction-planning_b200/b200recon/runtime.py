@@ -76,6 +76,12 @@ def ctx(device=None):
     return c
 
 
+def new_context(device=None):
+    """A further library context on `device` (own scratch, own side/copy streams, own extraction state): one per
+    z-slab when several slabs of a cube live in ONE process (parallel.LocalSlabs)."""
+    return Context(default_device() if device is None else int(device))
+
+
 def ptr(tensor):
     return C.c_void_p(0 if tensor is None else tensor.data_ptr())
 

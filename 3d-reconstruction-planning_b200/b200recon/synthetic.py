@@ -49,6 +49,21 @@ def orbit_poses(n_frames, radius=0.5, elevation_deg=30.0, target=(0.0, 0.0, 0.02
     return out
 
 
+def main_orbit_poses(n_images=12, object_point=(0.0, 0.0, 0.0), circ_rad=0.3, circ_height=0.15, path_disc=500):
+    """The simulator's camera path (main.py:68-136): a semicircle of radius 0.3 m in the vertical plane through the
+    object at azimuth 3*pi/4, centre shifted 0.15*cos(pi/4) towards -x/-y and 0.15 m up, discretised into 500 waypoints,
+    of which `img_total = 12` are photographed at equal time steps (main.py:213-232, `io.select_waypoints`).  The
+    camera looks at the object with up = +z (bullet_camera.py:56-62 `computeViewMatrix(eye, target, [0,0,1])`).
+    Returns camera->world 4x4 poses (camera axes +z forward, +x right, +y down)."""
+    from .io import select_waypoints
+    o = np.asarray(object_point, np.float64)
+    a = np.linspace(0.0, np.pi, path_disc)
+    x = o[0] - 0.15 * np.cos(np.pi / 4) + circ_rad * np.cos(a) * np.cos(3 * np.pi / 4)
+    y = o[1] - 0.15 * np.cos(np.pi / 4) + circ_rad * np.cos(a) * np.sin(3 * np.pi / 4)
+    z = circ_height + o[2] + circ_rad * np.sin(a)
+    return [look_at((x[i], y[i], z[i]), o) for i in select_waypoints(path_disc, n_images)]
+
+
 def extrinsic_from_pose(cam_to_world):
     """Open3D extrinsic = world->camera."""
     return np.linalg.inv(np.asarray(cam_to_world, np.float64))

@@ -65,6 +65,7 @@ int b2r_ctx_destroy(b2r_ctx* c) {
     for (auto& f : c->fslot) {
         b2r::Scratch* fs[] = {&f.dm, &f.rgba, &f.mip, &f.hdr, &f.rec, &f.counters, &f.raw_depth, &f.raw_color};
         for (auto* s : fs) s->release();
+        if (f.h_stage) cudaFreeHost(f.h_stage);
         if (f.ev_plan) cudaEventDestroy(f.ev_plan);
         if (f.ev_items) cudaEventDestroy(f.ev_items);
         if (f.ev_h2d) cudaEventDestroy(f.ev_h2d);

@@ -70,7 +70,9 @@ struct b2r_frame_slot {
     // frame i+1 runs while the caller's stream still prepares / plans frame i
     b2r::Scratch raw_depth, raw_color;
     cudaEvent_t ev_h2d = nullptr, ev_prep = nullptr;
-    bool prep_recorded = false;
+    bool prep_recorded = false, h2d_recorded = false;
+    void* h_stage = nullptr;         // pinned host staging of b2r_integrate_host_staged (pageable caller frames)
+    size_t h_stage_bytes = 0;
 };
 
 struct b2r_ctx {

@@ -46,9 +46,21 @@ CAMERAS = {"tsdf2048": "SYN_1280x720"}               # every other workload: the
 def camera(workload):
     from b200recon import synthetic as syn
     return getattr(syn, CAMERAS.get(workload, "D435_640x480"))
-# dram__bytes_read.sum + dram__bytes_write.sum of one integrate_items launch from the committed ncu --set full
-# capture of this command (profiles/r01_integrate_v11_ncu.txt); per launch, like roofline.achieved
-NCU_TRAFFIC = {"tsdf1024": 878633728 + 703095808}
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE integrate_items launch, from the committed `ncu --set full`
+    capture of this command (profiles/ncu_traffic.json: {workload: {bytes, profile, commit}}) -- per launch, like
+    roofline.achieved.  It is a profiler figure, not measured in this run: the source is named next to it, and
+    workloads without a capture report null."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        e = json.load(open(p)).get(workload)
+        if e:
+            return int(e["bytes"]), "%s (kernel source at commit %s)" % (e["profile"], e["commit"])
+    except Exception:
+        pass
+    return None, None
+
+
 B_UPD = 24  # algorithmic bytes per voxel update: float2 R+W (16) + packed colour R+W (8)  (BASELINE.md 4)
 
 
@@ -64,38 +76,70 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed regions.  nvidia-smi takes longer to start
-    than a short timed region lasts (256 steps on 8 GPUs = 22 ms), so one process runs across all timed passes of
-    the same load, every row is time-stamped when it arrives, and only rows that fall inside a timed window
-    (begin()/end() around the event-bracketed loop) are reported."""
+_NVML_POLL = r"""
+import sys, time
+import pynvml as N
+N.nvmlInit()
+key = sys.argv[1]
+try:
+    h = N.nvmlDeviceGetHandleByUUID(key if key.startswith("GPU-") else "GPU-" + key) if len(key) > 4 else N.nvmlDeviceGetHandleByIndex(int(key))
+except Exception:
+    h = N.nvmlDeviceGetHandleByIndex(int(sys.argv[2]))
+mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+period = float(sys.argv[3]) * 1e-3
+out = sys.stdout
+while True:
+    t = time.monotonic()
+    sm = N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)
+    r = N.nvmlDeviceGetCurrentClocksEventReasons(h)
+    out.write("%.6f %d %d %d\n" % (t, sm, mx, r))
+    out.flush()
+    time.sleep(period)
+"""
 
-    def __init__(self, device, period_ms=20):
+
+class ClockSampler:
+    """SM clock and clock-event reasons sampled DURING the timed regions.  A helper process polls NVML every
+    `period_ms` (nvidia-smi -lms cannot go below ~20 ms per row and takes longer to start than an 8-GPU timed region
+    lasts); every row carries the system-wide monotonic time at which it was taken, and only rows that fall inside a
+    timed window (begin()/end() around the event-bracketed loop) are reported."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, device, period_ms=1.0):
         self.device = device
         self.period_ms = period_ms
-        self.rows = []          # (monotonic time, fields)
+        self.rows = []          # (monotonic time, sm MHz, max MHz, reasons bitmask)
         self.windows = []       # [t0, t1]
         self.proc = None
 
     def start(self):
-        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        key = str(self.device)
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + q,
-                                          "--format=csv,noheader,nounits", "-lms", str(self.period_ms)],
+            import torch
+            u = getattr(torch.cuda.get_device_properties(self.device), "uuid", None)
+            if u is not None:
+                key = str(u)
+        except Exception:
+            pass
+        try:
+            self.proc = subprocess.Popen([sys.executable, "-c", _NVML_POLL, key, str(self.device), str(self.period_ms)],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
             return
         self.t = threading.Thread(target=self._read, daemon=True)
         self.t.start()
-        t_end = time.monotonic() + 3.0          # wait for the first row: the process is up and sampling
+        t_end = time.monotonic() + 10.0         # wait for the first row: the process is up and sampling
         while not self.rows and time.monotonic() < t_end and self.proc.poll() is None:
             time.sleep(0.01)
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append((time.monotonic(), [c.strip() for c in line.split(",")]))
+            f = line.split()
+            if len(f) == 4:
+                self.rows.append((float(f[0]), float(f[1]), float(f[2]), int(f[3])))
 
     def begin(self):
         self.windows.append([time.monotonic(), None])
@@ -104,21 +148,23 @@ class ClockSampler:
         self.windows[-1][1] = time.monotonic()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        if not self.proc or not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml sampler unavailable"], "samples": 0}
+        time.sleep(0.05)        # rows in flight in the pipe
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        ok = [r for t, r in self.rows if len(r) >= 6 and any(a <= t <= (b or t) for a, b in self.windows)]
-        sm = [float(r[0]) for r in ok if r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in ok if r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in ok for i in range(4) if r[2 + i] == "Active"})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+        ok = [r for r in self.rows if any(a <= r[0] <= (b or r[0]) for a, b in self.windows)]
+        sm = [r[1] for r in ok]
+        bits = 0
+        for r in ok:
+            bits |= r[3]
+        reasons = sorted(n for b, n in self.REASONS.items() if bits & b)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(r[2] for r in self.rows),
                 "reasons": reasons, "samples": len(sm), "timed_windows": len(self.windows),
-                "period_ms": self.period_ms}
+                "period_ms": self.period_ms, "source": "NVML polled by a helper process"}
 
 
 def orbit(workload):
@@ -153,9 +199,11 @@ def cpu_frames(workload, n, K):
     return out
 
 
-def cpu_volume(workload):
-    """Oracle volume over the largest x-range that fits comfortably in host RAM (Open3D parallelises
-    Integrate over x, so an x-range is the natural linear sample); returns (vol, scale)."""
+def cpu_volumes(workload, n_ranges=8):
+    """Oracle volumes over `n_ranges` x-ranges spread EVENLY over the cube (Open3D parallelises Integrate over x, so a
+    set of x-ranges is the natural linear sample; a single centred range over-represents the dense middle of the
+    cube -- the orbit looks at the cube centre).  Together they cover as many x planes as fit comfortably in host
+    RAM; returns (volumes, scale = R / planes covered, ranges)."""
     from b200recon import synthetic as syn
     from oracle import oracle as orc
     R, L, trunc, _ = orbit(workload)
@@ -164,33 +212,41 @@ def cpu_volume(workload):
     except Exception:
         avail = 8 << 30
     per_x = R * R * 32  # tsdf f32 + weight f32 + colour 3 x f64
-    nx = int(min(R, max(8, (min(avail // 3, 6 << 30)) // per_x)))
-    x0 = (R - nx) // 2  # centred range: the orbit looks at the cube centre
-    vol = orc.UniformTSDFVolume(L, R, trunc, 1, syn.volume_origin(L), x_range=(x0, x0 + nx))
-    return vol, R / nx, (x0, x0 + nx)
+    nx = int(min(R, max(n_ranges, (min(avail // 3, 6 << 30)) // per_x)))
+    n_ranges = max(1, min(n_ranges, nx))
+    w = max(1, nx // n_ranges)
+    ranges = []
+    for k in range(n_ranges):
+        x0 = int((k + 0.5) * R / n_ranges - 0.5 * w)
+        x0 = max(0, min(R - w, x0))
+        ranges.append((x0, x0 + w))
+    vols = [orc.UniformTSDFVolume(L, R, trunc, 1, syn.volume_origin(L), x_range=r) for r in ranges]
+    return vols, R / float(w * n_ranges), ranges
 
 
 def run_cpu(workload, steps, warmup, K, budget_s=25.0):
-    """frames/s of the oracle; each step = one frame on the sampled x-range, scaled linearly to R."""
+    """frames/s of the oracle; each step = one frame integrated into every sampled x-range, scaled linearly to R."""
     kt = (K["fx"], K["fy"], K["cx"], K["cy"])
     cpu_threads()
-    vol, scale, xr = cpu_volume(workload)
+    vols, scale, xr = cpu_volumes(workload)
     frames = cpu_frames(workload, max(1, min(8, steps)), K)
     for i in range(max(1, warmup)):
         d, c, e = frames[i % len(frames)]
-        vol.integrate(d, c, kt, e)
+        for v in vols:
+            v.integrate(d, c, kt, e)
     t0 = time.perf_counter()
     n = upd = 0
     while n < steps and (time.perf_counter() - t0) < budget_s:
         d, c, e = frames[n % len(frames)]
-        upd += vol.integrate(d, c, kt, e)
+        for v in vols:
+            upd += v.integrate(d, c, kt, e)
         n += 1
     dt = time.perf_counter() - t0
     R = WORKLOADS[workload][0]
     fps = n / (dt * scale)
-    sample = "%d frames of %s, x-range [%d,%d) of %d (time scaled x%.2f to the full cube)" % (n, workload, xr[0], xr[1],
-                                                                                             R, scale)
-    return fps, upd / dt, n, sample, dt
+    sample = "%d frames of %s, %d x-ranges of %d planes spread evenly over [0,%d) (first at x=%d; time scaled x%.2f to the full cube)" % (
+        n, workload, len(xr), xr[0][1] - xr[0][0], R, xr[0][0], scale)
+    return fps, upd * scale / dt, n, sample, dt
 
 
 def run_cpu_icp(K, max_dist=0.004):
@@ -351,6 +407,18 @@ def run_gpu(args):
         k = i % nf
         vol.integrate_host(d16_h[k], rgb_h[k], intr, exts[k])
 
+    # numpy (pageable) copies for the Open3D-named arm: what cv2.imread / np.load hand to stitcher.py
+    d16_np = d16_h.numpy()
+    rgb_np = rgb_h.numpy()
+    G = o3d.geometry
+
+    def step_o3d(i):
+        # the call sequence of stitcher.py:34-42 followed by north_star's integrate(rgbd, intrinsic, extrinsic)
+        k = i % nf
+        rgbd = G.RGBDImage.create_from_color_and_depth(G.Image(rgb_np[k]), G.Image(d16_np[k]), depth_scale=1000.0,
+                                                       depth_trunc=3.0, convert_rgb_to_intensity=False)
+        vol.integrate(rgbd, intr, exts[k])
+
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -402,6 +470,8 @@ def run_gpu(args):
     c_ms, upd, _ = timed(step_dev, args.steps, args.warmup)
     upd_k_local = timed.local_updates
     e_ms, e_upd, _ = timed(step_e2e, args.steps, args.warmup)
+    o_ms, o_upd, _ = timed(step_o3d, args.steps, args.warmup)
+    assert o_upd == e_upd == upd, "the three arms integrated different voxel sets: %r" % ((upd, e_upd, o_upd),)
     if os.environ.get("B2R_BENCH_DIAG"):        # where the e2e step spends its extra time (not part of the JSON contract)
         vol.count_updates = False
         n_ms, _, _ = timed(step_e2e, args.steps, args.warmup)
@@ -413,30 +483,40 @@ def run_gpu(args):
     mirror = ctx.updates_mirror()
     assert mirror == vol.updates(), "host mirror of the step result disagrees with the device counter"
 
-    # ---- the metric's other halves: ICP pairs/s (BASELINE config 4) and mesh extraction of the volume just built ----
+    # ---- the metric's other halves: mesh extraction of the volume just built (sharded: halo exchange -> per-slab
+    #      marching cubes -> seam -> gather on rank 0) and ICP pairs/s (BASELINE config 4, both radii) ----
     extra = {}
     if not args.no_extras:
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import bench_extra
-        try:
-            extra["mesh"] = bench_extra.mesh_bench(vol) if (world == 1 and R <= 1024) else None
-        except Exception as e:  # e.g. out of memory for the mesh of a very large volume: report, do not hide
-            extra["mesh"] = {"error": str(e)}
+        if R <= 1024:
+            try:
+                extra["mesh"] = bench_extra.sharded_mesh_bench(vol, ranges, L / R)
+                if world == 1:
+                    extra["mesh"].update(bench_extra.mesh_bench(vol))
+            except Exception as e:  # e.g. out of memory for the mesh of a very large volume: report, do not hide
+                extra["mesh"] = {"error": repr(e)}
         vol.reset()
-        icp = bench_extra.icp_bench(args.icp_pairs, 0.004, rank=rank, world=world)
-        if world > 1:
-            t = torch.tensor([icp["ms"]], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            icp["ms"] = float(t.item())
-        icp["pairs"] = args.icp_pairs
-        icp["pairs_per_s"] = args.icp_pairs / (icp["ms"] * 1e-3)
-        icp["distribution"] = "pair p -> GPU p %% %d, no collective" % world
-        extra["icp"] = icp
+        for key, radius in (("icp", 0.004), ("icp_r0.05", 0.05)):
+            icp = bench_extra.icp_bench(args.icp_pairs, radius, rank=rank, world=world)
+            if world > 1:
+                t = torch.tensor([icp["ms"]], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                icp["ms"] = float(t.item())
+            icp["pairs"] = args.icp_pairs
+            icp["pairs_per_s"] = args.icp_pairs / (icp["ms"] * 1e-3)
+            icp["distribution"] = "pair p -> GPU p %% %d, no collective" % world
+            extra[key] = icp
         if world == 1 and R <= 1024:
             try:
                 extra["scalable"] = bench_extra.scalable_bench(1024, 64, 0.9)
             except Exception as e:
-                extra["scalable"] = {"error": str(e)}
+                extra["scalable"] = {"error": repr(e)}
+        if world == 1:      # BASELINE configs[0]: the fused ICP -> integrate -> mesh path on the 12 banana frames
+            try:
+                extra["banana12"], run_gpu.banana_frames = bench_extra.banana12_bench()
+            except Exception as e:
+                extra["banana12"] = {"error": repr(e)}
 
     out = None
     if rank == 0:
@@ -445,6 +525,7 @@ def run_gpu(args):
         upd_rank0_per_launch = upd_k_local / max(args.steps, 1)      # rank 0's own slab, its own kernel time
         alg_bytes = upd_rank0_per_launch * B_UPD + frame_bytes(K)
         achieved = alg_bytes / (k_ms_timed / max(args.steps, 1) * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic(args.workload) if world == 1 else (None, None)
         fps = args.steps / (ms * 1e-3)
         out = {
             "metric": "TSDF integration frames/s (%dx%d RGB-D into dense TSDF+colour volume)" % (K["width"], K["height"]),
@@ -461,20 +542,84 @@ def run_gpu(args):
             "clocks": clocks,
             "e2e": {"value": args.steps / (e_ms * 1e-3), "unit": "frames/s",
                     "h2d_bytes_per_step": int(d16_h[0].numel() * 2 + rgb_h[0].numel()), "d2h_bytes_per_step": 8,
-                    "note": "host frames in pinned memory; H2D copies, conversion and planning of frame i+1 overlap "
-                            "the streaming kernel of frame i (library side stream)",
+                    "note": "integrate_host: host frames in pinned memory; H2D copies, conversion and planning of "
+                            "frame i+1 overlap the streaming kernel of frame i (library side stream)",
                     "voxel_updates_per_s": e_upd / (e_ms * 1e-3)},
+            "e2e_o3d": {"value": args.steps / (o_ms * 1e-3), "unit": "frames/s",
+                        "h2d_bytes_per_step": int(d16_h[0].numel() * 2 + rgb_h[0].numel()), "d2h_bytes_per_step": 8,
+                        "note": "the Open3D-named call surface of stitcher.py:34-42 + north_star: numpy (pageable) "
+                                "uint16 depth + uint8 colour -> geometry.Image x2 -> RGBDImage.create_from_color_and_depth"
+                                "(convert_rgb_to_intensity=False) -> vol.integrate(rgbd, intrinsic, extrinsic)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC.get(args.workload) if world == 1 else None, "kernel": "integrate_items_kernel", "peak_source": peak_src,
+                         "traffic": traffic, "traffic_source": traffic_src,
+                         "kernel": "integrate_items_kernel", "peak_source": peak_src,
                          "kernel_ms_per_launch": k_ms_timed / max(args.steps, 1),
                          "alg_bytes_per_launch": alg_bytes, "bytes_per_update": B_UPD,
-                         "frac_of_nominal_8TBs": achieved / 8000.0},
+                         "frac_of_nominal_8TBs": achieved / 8000.0,
+                         # the same algorithmic bytes over the WHOLE step (prepare + plan + streaming kernel + hand-offs)
+                         "step_achieved": alg_bytes / (ms / args.steps * 1e-3) / 1e9,
+                         "step_frac": alg_bytes / (ms / args.steps * 1e-3) / 1e9 / peak,
+                         "step_frac_of_nominal_8TBs": alg_bytes / (ms / args.steps * 1e-3) / 1e9 / 8000.0},
+            "notes": {"voxel_updates": "counted in a separate pass of the same steps with the counting kernel variant "
+                                       "(Open3D's integrate returns nothing); the timed `value` pass runs without the count",
+                      "parity": "bit-exact against oracle/ (a restatement of Open3D 0.18; UNPINNED against the real "
+                                "Open3D binary, which cannot be installed here)"},
         }
         out.update(extra)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return out
+
+
+def main_banana12(args, rank):
+    """BASELINE configs[0] as its own line: the fused path (ICP pose -> integrate -> mesh) over the 12 banana frames.
+    A step = one frame through pipelines.fusion.fuse_sequence, host frames in, every copy inside (value == e2e: the
+    path has no device-resident variant -- each registration blocks on its result like stitcher.py's loop).  One GPU:
+    the sequence is strictly serial (frame i registers against the model of frames < i), ranks > 0 exit."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_extra
+    metric = "fused ICP -> TSDF integrate -> mesh frames/s (12 x 640x480 banana frames, BASELINE configs[0])"
+    if args.impl == "reference":
+        import torch  # the frames come from the GPU ray caster when there is a GPU, else from its CPU twin
+        if torch.cuda.is_available():
+            frames = bench_extra.banana12_frames()
+        else:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import helpers as hp
+            frames = hp.banana_frames(12, 640, 480)
+        cpu_threads()
+        c = bench_extra.banana12_cpu(frames)
+        emit({"impl": "reference", "metric": metric, "value": c["frames_per_s"], "unit": "frames/s", "n_gpus": args.gpus,
+              "gpus_used": 0, "steps": 12, "warmup": 0, "ms_per_step": c["sequence_ms"] / 12, "higher_is_better": True,
+              "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+              "config": {"workload": "banana12"}, "cpu_baseline": c,
+              "e2e": {"value": c["frames_per_s"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+        return
+    import torch
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
+    sampler.start()
+    sampler.begin()
+    g, frames = bench_extra.banana12_bench(reps=max(1, min(args.steps, 5)))
+    sampler.end()
+    clocks = sampler.stop()
+    K = frames[0]
+    out = {"metric": metric, "value": g["frames_per_s"], "unit": "frames/s", "n_gpus": 1, "steps": 12, "warmup": 12,
+           "ms_per_step": g["sequence_ms"] / 12, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic", "config": {"workload": "banana12", "detail": g["workload"]},
+           "gpu_launches": g["gpu_launches_per_sequence"], "clocks": clocks,
+           "e2e": {"value": g["frames_per_s"], "unit": "frames/s",
+                   "h2d_bytes_per_step": int(K["width"] * K["height"] * 5), "d2h_bytes_per_step": 16 * 8 + 16,
+                   "note": "wall clock over the whole sequence incl. mesh read-back; value == e2e"},
+           "roofline": None, "quality": {k: v for k, v in g.items() if k not in ("workload", "sequence_ms", "frames_per_s")}}
+    if not args.no_cpu_baseline:
+        cpu_threads()
+        out["cpu_baseline"] = bench_extra.banana12_cpu(frames)
+        out["cpu_baseline"]["value"], out["cpu_baseline"]["unit"] = out["cpu_baseline"]["frames_per_s"], "frames/s"
+    emit(out)
 
 
 def emit(obj):
@@ -496,7 +641,7 @@ def main():
     ap.add_argument("--steps", type=int, default=256)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="tsdf1024", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="tsdf1024", choices=sorted(WORKLOADS) + ["banana12"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--equal-slabs", action="store_true", help="N > 1: equal plane counts instead of work-balanced slabs")
     ap.add_argument("--emulate-rank", default="", help="r/N: run rank r's slab of an N-way split on one GPU (tuning aid)")
@@ -505,6 +650,8 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
+    if args.workload == "banana12":
+        return main_banana12(args, rank)
     K = camera(args.workload)
 
     if args.impl == "reference":
@@ -515,7 +662,7 @@ def main():
         R = WORKLOADS[args.workload][0]
         emit(({
             "impl": "reference", "metric": "TSDF integration frames/s (%dx%d RGB-D into dense TSDF+colour volume)" % (K["width"], K["height"]),
-            "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": n, "warmup": args.warmup,
+            "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "gpus_used": 0, "steps": n, "warmup": args.warmup,
             "ms_per_step": 1000.0 / fps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": {"workload": args.workload, "resolution": R},
             "voxel_updates_per_s": ups,
@@ -535,6 +682,10 @@ def main():
                 out["icp"]["cpu_baseline"] = run_cpu_icp(K)
             if isinstance(out.get("scalable"), dict) and "error" not in out["scalable"]:
                 out["scalable"]["cpu_baseline"] = run_cpu_scalable(K)
+            if isinstance(out.get("banana12"), dict) and "error" not in out["banana12"]:
+                sys.path.insert(0, os.path.join(ROOT, "tools"))
+                import bench_extra
+                out["banana12"]["cpu_baseline"] = bench_extra.banana12_cpu(run_gpu.banana_frames)
         emit(out)
 
 

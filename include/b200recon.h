@@ -103,11 +103,20 @@ int b2r_backproject(b2r_ctx* ctx, const float* d_depth, const uint8_t* d_color, 
 int b2r_integrate(b2r_ctx* ctx, const b2r_volume* vol, const float* d_depth, const void* d_color,
                   const b2r_intrinsic* K, const double* extrinsic, unsigned long long* d_updates, void* stream);
 /* Same, end to end from HOST frame buffers: H2D copy + depth conversion (depth_scale/depth_trunc as
- * in stitcher.py:40-41) + integrate.  h_depth dtype as in b2r_depth_to_float.  Host buffers should be
- * pinned for the copies to overlap; they must stay valid until the stream reaches this call. */
+ * in stitcher.py:40-41) + integrate.  h_depth dtype as in b2r_depth_to_float.  Host buffers must be PINNED
+ * (cudaMallocHost / torch pin_memory) and must stay valid and unmodified until the copy has completed: the copy
+ * runs on a stream owned by the context and `stream` is ordered after it, so any later synchronisation of `stream`
+ * (an event recorded on it after this call, b2r_ctx_sync) covers it.  Pageable memory: use the _staged variant. */
 int b2r_integrate_host(b2r_ctx* ctx, const b2r_volume* vol, const void* h_depth, int depth_dtype,
                        const uint8_t* h_color, const b2r_intrinsic* K, const double* extrinsic, double depth_scale,
                        double depth_trunc, unsigned long long* d_updates, void* stream);
+/* Same for PAGEABLE host frames (numpy arrays from cv2.imread / np.load as stitcher.py:219-220,250-251 produce them,
+ * or geometry.Image buffers): the frame is first copied into a pinned staging buffer owned by the context (one per
+ * frame slot), so the H2D transfer is an asynchronous DMA overlapping the previous frame's kernels, and the caller's
+ * buffers may be freed or overwritten as soon as the call returns. */
+int b2r_integrate_host_staged(b2r_ctx* ctx, const b2r_volume* vol, const void* h_depth, int depth_dtype,
+                              const uint8_t* h_color, const b2r_intrinsic* K, const double* extrinsic, double depth_scale,
+                              double depth_trunc, unsigned long long* d_updates, void* stream);
 /* O3D pipelines.integration.ScalableTSDFVolume.integrate(rgbd, intrinsic, extrinsic) -- SURVEY.md section 8 row f4
  * / A.3 last bullet (Open3D 0.18 ScalableTSDFVolume::Integrate; no call site in the reference, named by
  * north_star next to UniformTSDFVolume).  Open3D's hash of unit_resolution^3-voxel units is laid out at its place

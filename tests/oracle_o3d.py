@@ -131,6 +131,37 @@ class _Intrinsic:
         self.width, self.height, self.fx, self.fy, self.cx, self.cy = width, height, fx, fy, cx, cy
 
 
+class _Mesh:
+    def __init__(self, V, T, Cc):
+        self.vertices, self.triangles = V, T
+        self.vertex_colors = Cc if Cc is not None else np.zeros((0, 3))
+
+
+class _ColorType:
+    NoColor, RGB8, Gray32 = 0, 1, 2
+
+
+class _UniformTSDFVolume:
+    """pipelines.integration.UniformTSDFVolume on the oracle (recon_oracle.cpp)."""
+
+    def __init__(self, length, resolution, sdf_trunc, color_type=1, origin=(0.0, 0.0, 0.0)):
+        self.v = orc.UniformTSDFVolume(length, resolution, sdf_trunc, int(color_type), origin)
+        self.color_type = int(color_type)
+
+    def integrate(self, rgbd, intrinsic, extrinsic):
+        K = (intrinsic.fx, intrinsic.fy, intrinsic.cx, intrinsic.cy)
+        return self.v.integrate(rgbd.depth, rgbd.color if self.color_type else None, K, np.asarray(extrinsic, np.float64))
+
+    def extract_triangle_mesh(self):
+        return _Mesh(*self.v.extract_triangle_mesh())
+
+    def extract_point_cloud(self):
+        P, N, Cc = self.v.extract_point_cloud()
+        out = PointCloud()
+        out._p, out._n, out._c = P, N, (Cc if Cc is not None and len(Cc) == len(P) else None)
+        return out
+
+
 geometry = types.SimpleNamespace(Image=_Image, RGBDImage=types.SimpleNamespace(create_from_color_and_depth=_create_rgbd),
                                  PointCloud=PointCloud, KDTreeSearchParamHybrid=_Hybrid)
 utility = types.SimpleNamespace(Vector3dVector=lambda a: np.asarray(a, np.float64))
@@ -138,4 +169,5 @@ camera = types.SimpleNamespace(PinholeCameraIntrinsic=_Intrinsic)
 pipelines = types.SimpleNamespace(registration=types.SimpleNamespace(
     registration_colored_icp=_colored, registration_icp=_icp, compute_fpfh_feature=lambda pcd, sp: None,
     TransformationEstimationForColoredICP=lambda: None, TransformationEstimationPointToPoint=_P2P,
-    TransformationEstimationPointToPlane=_P2L, ICPConvergenceCriteria=_Criteria))
+    TransformationEstimationPointToPlane=_P2L, ICPConvergenceCriteria=_Criteria),
+    integration=types.SimpleNamespace(UniformTSDFVolume=_UniformTSDFVolume, TSDFVolumeColorType=_ColorType))

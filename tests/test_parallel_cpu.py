@@ -199,3 +199,35 @@ def test_check_same_ranges_tiling_without_group():
         with pytest.raises(RuntimeError):
             parallel.check_same_ranges(bad, 64)
     assert np.array_equal(parallel.agree_plane_work([1.0, 2.0]), [1.0, 2.0])
+
+
+def test_mesh_checksum_is_order_and_numbering_independent():
+    """parallel.mesh_checksum (the digest bench.py prints for the N-GPU mesh): invariant under vertex order, triangle
+    order, vertex renumbering and the start corner of a triangle; sensitive to orientation, to a moved vertex and to
+    a dropped triangle; degenerate triangles (repeated corners, which Open3D keeps) included."""
+    rng = np.random.default_rng(0)
+    V = rng.uniform(-1, 1, (1000, 3))
+    T = rng.integers(0, 1000, (3000, 3))
+    T[:50, 1] = T[:50, 0]
+    a = parallel.mesh_checksum(V, T, 1e-7)
+    perm = rng.permutation(1000)
+    inv = np.empty(1000, np.int64)
+    inv[perm] = np.arange(1000)
+    T2 = np.roll(inv[T], 1, axis=1)[rng.permutation(3000)]
+    assert parallel.mesh_checksum(V[perm], T2, 1e-7) == a
+    T3 = T2.copy()
+    T3[100] = T3[100][::-1]
+    assert parallel.mesh_checksum(V[perm], T3, 1e-7) != a
+    V4 = V.copy()
+    V4[7, 1] += 1e-6
+    assert parallel.mesh_checksum(V4, T, 1e-7)["vertex_sum"] != a["vertex_sum"]
+    assert parallel.mesh_checksum(V, T[:-1], 1e-7)["triangle_sum"] != a["triangle_sum"]
+    e = parallel.mesh_checksum(np.zeros((0, 3)), np.zeros((0, 3), np.int64), 1e-7)
+    assert e["vertices"] == 0 and e["triangle_sum"] == "0" * 16
+
+
+def test_local_slabs_rejects_bad_partitions():
+    with pytest.raises(RuntimeError):
+        parallel.LocalSlabs(1.0, 32, 0.1, z_ranges=[(0, 10), (12, 32)])
+    with pytest.raises(RuntimeError):
+        parallel.LocalSlabs(1.0, 32, 0.1, z_ranges=[(0, 1), (1, 32)])          # thinner than the halo

@@ -102,6 +102,171 @@ def mesh_bench(vol, reps=2):
             "point_cloud_ms": ms_p, "points": int(p[0].shape[0])}
 
 
+def sharded_mesh_bench(vol, ranges, voxel_length):
+    """extract_triangle_mesh of the z-slab sharded cube through parallel.SlabVolume (every rank calls this with its own
+    slab `vol` = slab `ranges[rank]`): halo exchange of {tsdf,w}/colour planes -> per-slab marching cubes with global
+    vertex ids -> seam plane of the id table -> gather on rank 0.  CUDA-event time per phase (max over ranks), the
+    gathered counts and an order-independent digest of the mesh (parallel.mesh_checksum at 1e-4 voxel): the digest
+    of the N-GPU mesh must equal the 1-GPU one.  With one rank the exchanges are no-ops."""
+    import torch
+    import torch.distributed as dist
+    from b200recon import parallel
+    rank, world = parallel.world_info()
+    sv = parallel.SlabVolume(vol.length, vol.resolution, vol.sdf_trunc, vol.color_type, vol.origin, z_ranges=ranges,
+                             local=vol)
+    sv.extract_triangle_mesh()                       # warm-up: scratch allocation, NCCL channel set-up
+    sv._halo_valid = False
+    sv.timings = {"on": True}
+    t0 = time.perf_counter()
+    mesh = sv.extract_triangle_mesh()
+    wall = (time.perf_counter() - t0) * 1e3
+    keys = ["halo_ms", "count_ms", "seam_ms", "emit_ms", "gather_ms"]
+    tm = torch.tensor([sv.timings.get(k, 0.0) for k in keys] + [wall], dtype=torch.float64, device=vol._ctx.tdev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    tm = tm.cpu().tolist()
+    out = {k: v for k, v in zip(keys, tm[:-1])}
+    out["sharded_mesh_ms"] = sum(tm[:-1])
+    out["sharded_mesh_wall_ms"] = tm[-1]
+    out["slabs"] = world
+    out["per_slab_vertices"] = [int(v) for v in sv.last_counts[:, 0]]
+    out["per_slab_triangles"] = [int(v) for v in sv.last_counts[:, 1]]
+    out["exchange"] = ("none (single slab)" if world == 1 else
+                       "NCCL send/recv: %d+%d halo planes of {tsdf,w}+colour per seam, 1 vertex-id plane per seam, "
+                       "vertices/triangles to rank 0" % (2, 1))
+    if rank == 0:
+        V, T = np.asarray(mesh.vertices), np.asarray(mesh.triangles)
+        out["checksum"] = parallel.mesh_checksum(V, T, 1e-4 * voxel_length)
+        out["vertices"], out["triangles"] = int(len(V)), int(len(T))
+    return out
+
+
+BANANA_PLY = os.path.join(ROOT, "tests", "golden", "banana_poisson_nontextured.ply")
+
+
+def banana12_frames(K=None, n_images=12):
+    """BASELINE configs[0]: the 12 pictures main.py:213-232 takes on its semicircular camera path (main.py:68-136) of
+    the YCB banana on the floor, ray-cast on the GPU from the committed mesh (the reference's own frames are not
+    committed; its GL camera is unavailable on this box).  Host numpy frames, as stitcher.py's loaders return them."""
+    from b200recon import synthetic as syn, runtime
+    K = K or syn.D435_640x480
+    tris = syn.load_banana_triangles(BANANA_PLY)
+    tdev = runtime.to_device(tris)
+    poses = syn.main_orbit_poses(n_images)
+    cols, deps = [], []
+    for p in poses:
+        d16, rgb = syn.render_frame(p, K, tris_dev=tdev, tris=tris, checker=0.04)
+        cols.append(rgb.cpu().numpy())
+        deps.append(d16.cpu().numpy())
+    return K, cols, deps, poses, tris
+
+
+def _perturbed(poses, rot_sigma=0.004, trans_sigma=0.003, seed=3):
+    """the planned trajectory as a robot reports it (wtraj.txt, main.py:156-165): off by a small random SE(3) per pose"""
+    rng = np.random.default_rng(seed)
+    out = []
+    for p in poses:
+        w = rng.normal(0, rot_sigma, 3)
+        th = np.linalg.norm(w)
+        Kx = np.array([[0, -w[2], w[1]], [w[2], 0, -w[0]], [-w[1], w[0], 0]])
+        Rw = np.eye(3) + (np.sin(th) / th) * Kx + ((1 - np.cos(th)) / th ** 2) * (Kx @ Kx)
+        q = np.array(p, np.float64)
+        q[:3, :3] = Rw @ q[:3, :3]
+        q[:3, 3] += rng.normal(0, trans_sigma, 3)
+        out.append(q)
+    out[0] = np.array(poses[0], np.float64)
+    return out
+
+
+BANANA_CFG = dict(resolution=256, voxel=0.002, trunc=0.01, reg_voxel=0.004, max_dist=0.01, estimation="colored",
+                  target="model")
+
+
+def _banana_quality(res, poses, tris, voxel):
+    from scipy.spatial import cKDTree
+    et, er = [], []
+    for T, P in zip(res.poses, poses):
+        et.append(float(np.linalg.norm(T[:3, 3] - P[:3, 3])))
+        c = (np.trace(T[:3, :3].T @ P[:3, :3]) - 1.0) / 2.0
+        er.append(float(np.degrees(np.arccos(np.clip(c, -1.0, 1.0)))))
+    V = np.asarray(res.mesh.vertices)
+    rng = np.random.default_rng(0)
+    a = np.asarray(tris, np.float64).reshape(-1, 3, 3)
+    r1, r2 = rng.random((len(a), 20, 1)), rng.random((len(a), 20, 1))
+    m = r1 + r2 > 1
+    r1, r2 = np.where(m, 1 - r1, r1), np.where(m, 1 - r2, r2)
+    S = (a[:, None, 0] + r1 * (a[:, None, 1] - a[:, None, 0]) + r2 * (a[:, None, 2] - a[:, None, 0])).reshape(-1, 3)
+    obj = V[V[:, 2] > 2 * voxel]
+    d, _ = cKDTree(S).query(obj)
+    return {"pose_err_mm_max": 1e3 * max(et), "pose_err_mm_last": 1e3 * et[-1], "pose_err_deg_max": max(er),
+            "mesh_vertices": int(len(V)), "mesh_triangles": int(len(res.mesh.triangles)),
+            "object_vertices": int(len(obj)), "surface_dist_mm_median": 1e3 * float(np.median(d)),
+            "surface_dist_mm_p95": 1e3 * float(np.percentile(d, 95)), "voxel_mm": 1e3 * voxel}
+
+
+def banana12_bench(reps=3, frames=None):
+    """The fused path (pipelines.fusion.fuse_sequence: create_point_cloud_from_rgbd -> ICP -> integrate -> ... ->
+    extract_triangle_mesh) on BASELINE configs[0], end to end from host frames, wall clock (every step blocks on its
+    result, like stitcher.py's loop)."""
+    import torch
+    import b200recon as o3d
+    from b200recon.pipelines import fusion
+    K, cols, deps, poses, tris = frames or banana12_frames()
+    cfg = BANANA_CFG
+    R, vl = cfg["resolution"], cfg["voxel"]
+    L = R * vl
+    intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], K["fx"], K["fy"], K["cx"], K["cy"])
+    integ = o3d.pipelines.integration
+    init = _perturbed(poses)
+    vol = integ.UniformTSDFVolume(L, R, cfg["trunc"], integ.TSDFVolumeColorType.RGB8, (-L / 2, -L / 2, -0.1 * L))
+    ctx = vol._ctx
+
+    def run():
+        vol.reset()
+        return fusion.fuse_sequence(cols, deps, intr, vol, init_poses=init, max_correspondence_distance=cfg["max_dist"],
+                                    registration_voxel_size=cfg["reg_voxel"], estimation=cfg["estimation"],
+                                    target=cfg["target"])
+    run()                                   # warm-up: scratch allocation
+    torch.cuda.synchronize()
+    l0 = ctx.launch_count()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        res = run()
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / reps
+    out = {"workload": "banana12: %d frames %dx%d on the main.py camera path, fuse_sequence(%s ICP frame-to-%s, %g mm "
+                       "registration clouds, r = %g m) into %d^3 @ %g mm + mesh" % (
+                           len(cols), K["width"], K["height"], cfg["estimation"], cfg["target"], 1e3 * cfg["reg_voxel"],
+                           cfg["max_dist"], R, 1e3 * vl),
+           "sequence_ms": 1e3 * dt, "frames_per_s": len(cols) / dt, "gpu_launches_per_sequence": (ctx.launch_count() - l0) // reps,
+           "iterations_mean": float(np.mean([r.iterations for r in res.registrations[1:]]))}
+    out.update(_banana_quality(res, poses, tris, vl))
+    return out, (K, cols, deps, poses, tris)
+
+
+def banana12_cpu(frames):
+    """The same sequence on the oracle port (tests/oracle_o3d.py wraps oracle/ in Open3D's names) on the host cores."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_o3d as A
+    from b200recon.pipelines import fusion
+    from oracle import oracle as orc
+    K, cols, deps, poses, tris = frames
+    cfg = BANANA_CFG
+    R, vl = cfg["resolution"], cfg["voxel"]
+    L = R * vl
+    intr = A.camera.PinholeCameraIntrinsic(K["width"], K["height"], K["fx"], K["fy"], K["cx"], K["cy"])
+    vol = A.pipelines.integration.UniformTSDFVolume(L, R, cfg["trunc"], 1, (-L / 2, -L / 2, -0.1 * L))
+    t0 = time.perf_counter()
+    res = fusion.fuse_sequence(cols, deps, intr, vol, init_poses=_perturbed(poses), max_correspondence_distance=cfg["max_dist"],
+                               registration_voxel_size=cfg["reg_voxel"], estimation=cfg["estimation"], target=cfg["target"],
+                               api=A)
+    dt = time.perf_counter() - t0
+    out = {"sequence_ms": 1e3 * dt, "frames_per_s": len(cols) / dt, "cores": orc.max_threads(), "kind": "port",
+           "sample": "the whole 12-frame sequence once"}
+    out.update(_banana_quality(res, poses, tris, vl))
+    return out
+
+
 def scalable_bench(resolution=1024, n_frames=64, radius=0.9, steps=None):
     """ScalableTSDFVolume.integrate (row f4): 640x480 frames of the bench orbit into 2 mm voxels, 16^3 units, stride 4,
     trunc 10 mm, frames resident in HBM.  Reports frames/s, touched units and updates per frame and the algorithmic
