@@ -52,6 +52,18 @@ class Context:
         _lib.check(_lib.load().b2r_ctx_kernel_time(self.handle, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def trace(self, max_calls):
+        """Start (max_calls > 0) / stop (0) the device-side timeline of integrate calls (b2r_ctx_trace)."""
+        _lib.check(_lib.load().b2r_ctx_trace(self.handle, int(max_calls)))
+
+    def trace_read(self, cap=4096):
+        """[n, 4, 2] uint64 ns: {start, end} of frame_prepare / integrate_plan / integrate_items per recorded call."""
+        import numpy as np
+        buf = (C.c_uint64 * (cap * 8))()
+        n = C.c_int(0)
+        _lib.check(_lib.load().b2r_ctx_trace_read(self.handle, buf, cap, C.byref(n)))
+        return np.frombuffer(buf, dtype=np.uint64)[: n.value * 8].reshape(n.value, 4, 2).copy()
+
     def join(self):
         """Order the current torch stream after every integration queued so far (their streaming kernels run on
         a stream owned by the library context).  Needed only before touching a volume's tensors directly."""

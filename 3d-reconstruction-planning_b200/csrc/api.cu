@@ -76,7 +76,7 @@ int b2r_ctx_destroy(b2r_ctx* c) {
     b2r::Scratch* all[] = {&c->frame_raw_depth, &c->frame_raw_color, &c->frame_f32,
                            &c->small, &c->scan_a, &c->scan_b, &c->mc_code, &c->mc_flags, &c->mc_block_counts,
                            &c->mc_vert_id, &c->pc_block_counts, &c->icp_a, &c->icp_b, &c->icp_c, &c->icp_d,
-                           &c->icp_e, &c->icp_f, &c->cl_a, &c->cl_b, &c->cl_c, &c->cl_d, &c->mc_live};
+                           &c->icp_e, &c->icp_f, &c->cl_a, &c->cl_b, &c->cl_c, &c->cl_d, &c->mc_live, &c->trace};
     for (auto* s : all) s->release();
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     if (c->pinned) cudaFreeHost(c->pinned);
@@ -109,6 +109,32 @@ int b2r_ctx_kernel_time(b2r_ctx* c, double* ms_total, int64_t* n_launches) {
     }
     *ms_total = tot;
     *n_launches = (int64_t)(c->ev_used / 2);
+    return 0;
+}
+
+int b2r_ctx_trace(b2r_ctx* c, int max_calls) {
+    B2R_CHECK(c, -1, "b2r_ctx_trace: NULL ctx");
+    B2R_CUDA(cudaSetDevice(c->device));
+    c->trace_on = false;
+    c->trace_n = 0;
+    if (max_calls <= 0) return 0;
+    if (c->trace.ensure((size_t)max_calls * 8 * sizeof(unsigned long long))) return -102;
+    B2R_CUDA(cudaDeviceSynchronize());
+    B2R_CUDA(cudaMemset(c->trace.ptr, 0, (size_t)max_calls * 8 * sizeof(unsigned long long)));
+    c->trace_cap = max_calls;
+    c->trace_on = true;
+    return 0;
+}
+
+int b2r_ctx_trace_read(b2r_ctx* c, unsigned long long* out, int cap_calls, int* n_calls) {
+    B2R_CHECK(c && out && n_calls, -1, "b2r_ctx_trace_read: NULL argument");
+    B2R_CUDA(cudaSetDevice(c->device));
+    B2R_CUDA(cudaDeviceSynchronize());
+    const int n = c->trace_n < cap_calls ? c->trace_n : cap_calls;
+    if (n > 0) B2R_CUDA(cudaMemcpy(out, c->trace.ptr, (size_t)n * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; ++i)
+        for (int k = 0; k < 8; k += 2) out[i * 8 + k] = out[i * 8 + k] ? ~out[i * 8 + k] : 0ull;   // stored as max(~start)
+    *n_calls = n;
     return 0;
 }
 

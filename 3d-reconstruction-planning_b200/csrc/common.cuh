@@ -73,6 +73,11 @@ struct b2r_frame_slot {
     bool prep_recorded = false, h2d_recorded = false;
     void* h_stage = nullptr;         // pinned host staging of b2r_integrate_host_staged (pageable caller frames)
     size_t h_stage_bytes = 0;
+    // The atomicMax levels of the pyramid, the frame maximum and the work-item counters must be zero before a frame is
+    // prepared.  The items kernel leaves them zeroed when it is done with them (its last warp), so in steady state no
+    // memset node sits between the kernels of consecutive frames; `clean` is false whenever that did not happen
+    // (fresh buffers, a frame prepared for the unit path, an error between prepare and launch).
+    bool clean = false;
 };
 
 struct b2r_ctx {
@@ -106,12 +111,29 @@ struct b2r_ctx {
     size_t ev_used = 0;
     void* pinned = nullptr;   // small pinned host buffer for result read-back
     size_t pinned_bytes = 0;
+    // optional device-side timeline (b2r_ctx_trace): per integrate call 8 uint64 = {~start, end} of frame_prepare,
+    // integrate_plan, integrate_items (+ 2 spare), %globaltimer nanoseconds, written by the kernels themselves
+    b2r::Scratch trace;
+    int trace_cap = 0, trace_n = 0;
+    bool trace_on = false;
 };
 
 namespace b2r {
 // Orders `st` after every items kernel launched so far (they run on the context's side stream).
 static inline cudaError_t join_side(b2r_ctx* ctx, cudaStream_t st) {
     return ctx->last_items ? cudaStreamWaitEvent(st, ctx->last_items, 0) : cudaSuccess;
+}
+// %globaltimer timeline hooks (no-ops when `tr` is NULL): start is kept as the maximum of ~t, i.e. the earliest block.
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void trace_begin(unsigned long long* tr) { if (tr) atomicMax(tr, ~gtimer_ns()); }
+__device__ __forceinline__ void trace_end(unsigned long long* tr) { if (tr) atomicMax(tr + 1, gtimer_ns()); }
+static inline unsigned long long* trace_row(b2r_ctx* ctx, int kernel) {
+    if (!ctx->trace_on || ctx->trace_n >= ctx->trace_cap) return nullptr;
+    return (unsigned long long*)ctx->trace.ptr + (size_t)ctx->trace_n * 8 + kernel * 2;
 }
 static inline cudaStream_t S(void* s) { return (cudaStream_t)s; }
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

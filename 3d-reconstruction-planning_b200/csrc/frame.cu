@@ -25,58 +25,90 @@ __global__ void depth_to_float_kernel(const void* __restrict__ depth, int dtype,
 
 // One pass per frame: metres depth (optionally converting from the raw dtype), the
 // depth->camera-distance multiplier of O3D CreateDepthToCameraDistanceMultiplierFloatImage
-// (float32, sqrtf(xx^2 + yy^2 + 1), same operation order) and the colour packed to one 32-bit word,
-// interleaved as one 16-byte pixel record {depth, multiplier, colour bits, 0} so the integrate kernel
-// fetches everything a voxel needs from the frame with a single 16-byte gather.
-__global__ void frame_prepare_kernel(const void* __restrict__ depth, int dtype, int convert, float scale, float trunc,
-                                     const void* __restrict__ color, int color_mode, int H, int W, float cx, float cy,
-                                     float ffl_inv_x, float ffl_inv_y, float2* __restrict__ px,
-                                     uint32_t* __restrict__ pcol,
-                                     const MipDesc M, unsigned int* __restrict__ mip,
-                                     unsigned int* __restrict__ dmax_bits) {
-    const int u = blockIdx.x * blockDim.x + threadIdx.x;
-    const int v = blockIdx.y;
-    float d = 0.0f;
+// (float32, sqrtf(xx^2 + yy^2 + 1), same operation order) as one 8-byte pixel record {depth, multiplier}, and
+// the colour packed to one 32-bit word in the volume's own format.
+//
+// A block is a 128 x 8 pixel strip (a thread = 8 pixels of a column, all 8 loads in flight together), so the
+// max-depth pyramid comes out of registers: level 0 (8 x 8 cells) is complete inside a warp and is STORED (no
+// atomics, no zero-fill needed); the strip contributes 16 atomicMax to levels 1..4 and the frame maximum instead
+// of the 320 a row-per-block kernel needs for the same pixels (those same-address atomics were most of the old
+// kernel's 13 us).  Levels 1..4 and the frame maximum must be zero on entry (see b2r_frame_slot::clean).
+__global__ void __launch_bounds__(128) frame_prepare_kernel(const void* __restrict__ depth, int dtype, int convert, float scale,
+                                                            float trunc, const void* __restrict__ color, int color_mode, int H,
+                                                            int W, float cx, float cy, float ffl_inv_x, float ffl_inv_y,
+                                                            float2* __restrict__ px, uint32_t* __restrict__ pcol, const MipDesc M,
+                                                            unsigned int* __restrict__ mip, unsigned int* __restrict__ dmax_bits,
+                                                            unsigned long long* __restrict__ tr) {
+    if (threadIdx.x == 0) trace_begin(tr);
+    const int u = blockIdx.x * 128 + threadIdx.x;
+    const int v0 = blockIdx.y * 8;
+    float m = 0.0f;
     if (u < W) {
-        const int64_t i = (int64_t)v * W + u;
-        d = load_depth_raw(depth, dtype, i);
-        if (convert) {
-            d = d / scale;
-            if (d >= trunc) d = 0.0f;
+        float d[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) d[r] = (v0 + r < H) ? load_depth_raw(depth, dtype, (int64_t)(v0 + r) * W + u) : 0.0f;
+        uint32_t c[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            c[r] = 0u;
+            if (v0 + r < H) {
+                const int64_t i = (int64_t)(v0 + r) * W + u;
+                if (color_mode == 1) {
+                    const uint8_t* p = (const uint8_t*)color + i * 3;
+                    // the volume's own packed format (10:10:10 fixed point, value * 4) so that the integrate kernel
+                    // unpacks frame and voxel colour with the same three instructions
+                    c[r] = ((uint32_t)p[0] << 2) | ((uint32_t)p[1] << 12) | ((uint32_t)p[2] << 22);
+                } else if (color_mode == 2) {
+                    c[r] = __float_as_uint(((const float*)color)[i]);
+                }
+            }
         }
         const float xx = ((float)u - cx) * ffl_inv_x;
-        const float yy = ((float)v - cy) * ffl_inv_y;
-        const float m = sqrtf(xx * xx + yy * yy + 1.0f);
-        uint32_t c = 0u;
-        if (color_mode == 1) {
-            const uint8_t* p = (const uint8_t*)color + i * 3;
-            // the volume's own packed format (10:10:10 fixed point, value * 4) so that the integrate kernel
-            // unpacks frame and voxel colour with the same three instructions
-            c = ((uint32_t)p[0] << 2) | ((uint32_t)p[1] << 12) | ((uint32_t)p[2] << 22);
-        } else if (color_mode == 2) {
-            c = __float_as_uint(((const float*)color)[i]);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (v0 + r < H) {
+                float dd = d[r];
+                if (convert) {
+                    dd = dd / scale;
+                    if (dd >= trunc) dd = 0.0f;
+                }
+                const float yy = ((float)(v0 + r) - cy) * ffl_inv_y;
+                const float mult = sqrtf(xx * xx + yy * yy + 1.0f);
+                const int64_t i = (int64_t)(v0 + r) * W + u;
+                px[i] = make_float2(dd, mult);
+                pcol[i] = c[r];
+                m = fmaxf(m, dd);      // (dd <= 0 and NaN never raise the maximum)
+            }
         }
-        px[i] = make_float2(d, m);
-        pcol[i] = c;
     }
-    // Max-depth pyramid (cells of 8, 16, 32, 64, 128 pixels; positive floats order like their bit patterns)
-    // and the frame-wide maximum.  The integrate kernel bounds the depth any voxel of a lane's z chunk can
-    // see by the maximum over the <= 2x2 cells covering the chunk's image footprint and skips voxels lying
-    // more than sdf_trunc behind it (hierarchical-z culling).  blockDim.x = 128: a warp is 32 pixels of a row.
-    float m = (d > 0.0f) ? d : 0.0f;
-    const int lane = threadIdx.x & 31;
-    const int u0 = u - lane;   // first pixel of this warp (multiple of 32)
+    // Max-depth pyramid (cells of 8, 16, 32, 64, 128 pixels; positive floats order like their bit patterns) and
+    // the frame-wide maximum.  The integrate kernels bound the depth a run of voxels can read by the maximum over
+    // the cells covering its image footprint and skip voxels more than sdf_trunc behind it (hierarchical z).
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cv = blockIdx.y;
 #pragma unroll
     for (int o = 1; o < 8; o <<= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if ((lane & 7) == 0 && m > 0.0f) atomicMax(&mip[M.off[0] + (v >> 3) * M.w[0] + (u >> 3)], __float_as_uint(m));
+    if ((lane & 7) == 0 && (u >> 3) < M.w[0]) mip[M.off[0] + cv * M.w[0] + (u >> 3)] = __float_as_uint(m);
     m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
-    if ((lane & 15) == 0 && m > 0.0f) atomicMax(&mip[M.off[1] + (v >> 4) * M.w[1] + (u >> 4)], __float_as_uint(m));
+    if ((lane & 15) == 0 && m > 0.0f) atomicMax(&mip[M.off[1] + (cv >> 1) * M.w[1] + (u >> 4)], __float_as_uint(m));
     m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 16));
-    if (lane == 0 && m > 0.0f) {
-#pragma unroll
-        for (int l = 2; l < B2R_MIP_LEVELS; ++l)
-            atomicMax(&mip[M.off[l] + (v >> (3 + l)) * M.w[l] + (u0 >> (3 + l))], __float_as_uint(m));
-        atomicMax(dmax_bits, __float_as_uint(m));
+    __shared__ float s_m[4];
+    if (lane == 0) {
+        s_m[warp] = m;
+        if (m > 0.0f) atomicMax(&mip[M.off[2] + (cv >> 2) * M.w[2] + (u >> 5)], __float_as_uint(m));
+    }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        const float m64 = fmaxf(s_m[threadIdx.x * 2], s_m[threadIdx.x * 2 + 1]);
+        if (m64 > 0.0f) atomicMax(&mip[M.off[3] + (cv >> 3) * M.w[3] + (blockIdx.x * 2 + threadIdx.x)], __float_as_uint(m64));
+        if (threadIdx.x == 0) {
+            const float m128 = fmaxf(fmaxf(s_m[0], s_m[1]), fmaxf(s_m[2], s_m[3]));
+            if (m128 > 0.0f) {
+                atomicMax(&mip[M.off[4] + (cv >> 4) * M.w[4] + blockIdx.x], __float_as_uint(m128));
+                atomicMax(dmax_bits, __float_as_uint(m128));
+            }
+            trace_end(tr);
+        }
     }
 }
 
@@ -101,16 +133,23 @@ int prepare_frame(b2r_ctx* ctx, b2r_frame_slot* slot, const void* d_depth, int d
     if (slot->dm.ensure(n * sizeof(float2))) return -102;
     if (slot->rgba.ensure(n * sizeof(uint32_t))) return -102;
     const MipDesc M = mip_desc(H, W);
-    if (slot->mip.ensure((size_t)(M.total + 1) * sizeof(float))) return -102;
-    B2R_CUDA(cudaMemsetAsync(slot->mip.ptr, 0, (size_t)(M.total + 1) * sizeof(float), stream));
+    const size_t mip_bytes = (size_t)(M.total + 1) * sizeof(float);
+    if (slot->mip.bytes < mip_bytes || slot->counters.bytes < 64) slot->clean = false;
+    if (slot->mip.ensure(mip_bytes)) return -102;
+    if (slot->counters.ensure(64)) return -102;
+    if (!slot->clean) {
+        B2R_CUDA(cudaMemsetAsync(slot->mip.ptr, 0, mip_bytes, stream));
+        B2R_CUDA(cudaMemsetAsync(slot->counters.ptr, 0, 64, stream));
+    }
+    slot->clean = false;      // set again by integrate_prepared once an items kernel that re-zeroes them is queued
     unsigned int* mip = (unsigned int*)slot->mip.ptr;
     unsigned int* dmax = mip + M.total;   // frame-wide maximum depth sits behind the pyramid
     const float ffl_inv_x = 1.0f / (float)K->fx, ffl_inv_y = 1.0f / (float)K->fy;
-    dim3 block(128), grid(cdiv(W, 128), H);
+    dim3 block(128), grid(cdiv(W, 128), cdiv(H, 8));
     frame_prepare_kernel<<<grid, block, 0, stream>>>(d_depth, dtype, convert, (float)depth_scale, (float)depth_trunc,
                                                      d_color, color_mode, H, W, (float)K->cx, (float)K->cy, ffl_inv_x,
                                                      ffl_inv_y, (float2*)slot->dm.ptr, (uint32_t*)slot->rgba.ptr, M,
-                                                     mip, dmax);
+                                                     mip, dmax, trace_row(ctx, 0));
     B2R_LAUNCH_CHECK(ctx);
     return 0;
 }

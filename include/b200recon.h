@@ -82,6 +82,13 @@ int b2r_ctx_updates_mirror(b2r_ctx* ctx, unsigned long long* out);
  * b2r_ctx_kernel_time is blocking: total milliseconds and number of launches collected. */
 int b2r_ctx_kernel_timing(b2r_ctx* ctx, int enable);
 int b2r_ctx_kernel_time(b2r_ctx* ctx, double* ms_total, int64_t* n_launches);
+/* Device-side timeline of the integrate calls (tuning / profiles/ evidence; the kernels write %globaltimer
+ * themselves, nothing is added to the streams).  b2r_ctx_trace(ctx, max_calls > 0) starts recording the next
+ * max_calls b2r_integrate* calls (blocking: synchronises the device), max_calls = 0 stops.  b2r_ctx_trace_read
+ * (blocking) copies, per recorded call, 8 uint64 nanosecond stamps: {start, end} of frame_prepare_kernel,
+ * integrate_plan_kernel, integrate_items_kernel, and two spare zeros (0 = kernel did not run). */
+int b2r_ctx_trace(b2r_ctx* ctx, int max_calls);
+int b2r_ctx_trace_read(b2r_ctx* ctx, unsigned long long* out, int cap_calls, int* n_calls);
 
 /* ---- images / back-projection (stitcher.py:34-46) --------------------------------------- */
 /* O3D Image.ConvertDepthToFloatImage(depth_scale, depth_trunc) inside
