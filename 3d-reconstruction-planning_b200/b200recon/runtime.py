@@ -57,12 +57,14 @@ class Context:
         _lib.check(_lib.load().b2r_ctx_trace(self.handle, int(max_calls)))
 
     def trace_read(self, cap=4096):
-        """[n, 4, 2] uint64 ns: {start, end} of frame_prepare / integrate_plan / integrate_items per recorded call."""
+        """([n, 4, 2] uint64 ns: {start, end} of frame_prepare / integrate_plan / integrate_items / integrate_cull per
+        recorded call, [n] live tiles, [n] work items)."""
         import numpy as np
-        buf = (C.c_uint64 * (cap * 8))()
+        buf = (C.c_uint64 * (cap * 16))()
         n = C.c_int(0)
         _lib.check(_lib.load().b2r_ctx_trace_read(self.handle, buf, cap, C.byref(n)))
-        return np.frombuffer(buf, dtype=np.uint64)[: n.value * 8].reshape(n.value, 4, 2).copy()
+        a = np.frombuffer(buf, dtype=np.uint64)[: n.value * 16].reshape(n.value, 16).copy()
+        return a[:, :8].reshape(n.value, 4, 2), (a[:, 8] >> np.uint64(32)).astype(np.int64), (a[:, 8] & np.uint64(0xffffffff)).astype(np.int64)
 
     def join(self):
         """Order the current torch stream after every integration queued so far (their streaming kernels run on

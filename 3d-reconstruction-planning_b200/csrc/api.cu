@@ -63,7 +63,7 @@ int b2r_ctx_destroy(b2r_ctx* c) {
     if (c->side) cudaStreamSynchronize(c->side);
     if (c->copy) cudaStreamSynchronize(c->copy);
     for (auto& f : c->fslot) {
-        b2r::Scratch* fs[] = {&f.dm, &f.rgba, &f.mip, &f.hdr, &f.rec, &f.counters, &f.raw_depth, &f.raw_color};
+        b2r::Scratch* fs[] = {&f.dm, &f.rgba, &f.mip, &f.hdr, &f.rec, &f.counters, &f.live, &f.raw_depth, &f.raw_color};
         for (auto* s : fs) s->release();
         if (f.h_stage) cudaFreeHost(f.h_stage);
         if (f.ev_plan) cudaEventDestroy(f.ev_plan);
@@ -118,9 +118,9 @@ int b2r_ctx_trace(b2r_ctx* c, int max_calls) {
     c->trace_on = false;
     c->trace_n = 0;
     if (max_calls <= 0) return 0;
-    if (c->trace.ensure((size_t)max_calls * 8 * sizeof(unsigned long long))) return -102;
+    if (c->trace.ensure((size_t)max_calls * 16 * sizeof(unsigned long long))) return -102;
     B2R_CUDA(cudaDeviceSynchronize());
-    B2R_CUDA(cudaMemset(c->trace.ptr, 0, (size_t)max_calls * 8 * sizeof(unsigned long long)));
+    B2R_CUDA(cudaMemset(c->trace.ptr, 0, (size_t)max_calls * 16 * sizeof(unsigned long long)));
     c->trace_cap = max_calls;
     c->trace_on = true;
     return 0;
@@ -131,9 +131,9 @@ int b2r_ctx_trace_read(b2r_ctx* c, unsigned long long* out, int cap_calls, int* 
     B2R_CUDA(cudaSetDevice(c->device));
     B2R_CUDA(cudaDeviceSynchronize());
     const int n = c->trace_n < cap_calls ? c->trace_n : cap_calls;
-    if (n > 0) B2R_CUDA(cudaMemcpy(out, c->trace.ptr, (size_t)n * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    if (n > 0) B2R_CUDA(cudaMemcpy(out, c->trace.ptr, (size_t)n * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     for (int i = 0; i < n; ++i)
-        for (int k = 0; k < 8; k += 2) out[i * 8 + k] = out[i * 8 + k] ? ~out[i * 8 + k] : 0ull;   // stored as max(~start)
+        for (int k = 0; k < 8; k += 2) out[i * 16 + k] = out[i * 16 + k] ? ~out[i * 16 + k] : 0ull;   // stored as max(~start)
     *n_calls = n;
     return 0;
 }

@@ -63,7 +63,8 @@ struct Scratch {
 #endif
 struct b2r_frame_slot {
     b2r::Scratch dm, rgba, mip;      // prepared frame: {depth, multiplier} pairs, colour words, max-depth pyramid
-    b2r::Scratch hdr, rec, counters; // work items of the frame and their two counters
+    b2r::Scratch hdr, rec, counters; // work items of the frame and their counters
+    b2r::Scratch live;               // tiles that survived the coarse cull
     cudaEvent_t ev_plan = nullptr, ev_items = nullptr;
     bool busy = false;               // ev_items has been recorded
     // host frames (b2r_integrate_host): raw depth/colour land here from the context's copy stream, so the H2D copy of
@@ -98,6 +99,12 @@ struct b2r_ctx {
     b2r::Scratch mc_code, mc_flags, mc_block_counts, mc_vert_id, mc_live;
     int64_t mc_nv = 0, mc_nt = 0;
     int mc_R = 0, mc_zb = 0, mc_ze = 0;
+    // Extraction is count -> emit against state kept here: the emit calls check that they see the SAME volume buffer
+    // and that nothing of this context has written a volume since the count (write_gen is bumped by every integrate /
+    // import / reset), else error -9 instead of silently stale ids and positions.
+    const void* mc_vol = nullptr;
+    const void* pc_vol = nullptr;
+    uint64_t write_gen = 1, mc_gen = 0, pc_gen = 0;
     // point extraction
     b2r::Scratch pc_block_counts;
     int64_t pc_n = 0;
@@ -111,8 +118,8 @@ struct b2r_ctx {
     size_t ev_used = 0;
     void* pinned = nullptr;   // small pinned host buffer for result read-back
     size_t pinned_bytes = 0;
-    // optional device-side timeline (b2r_ctx_trace): per integrate call 8 uint64 = {~start, end} of frame_prepare,
-    // integrate_plan, integrate_items (+ 2 spare), %globaltimer nanoseconds, written by the kernels themselves
+    // optional device-side timeline (b2r_ctx_trace): per integrate call 16 uint64 = {~start, end} of frame_prepare,
+    // integrate_plan, integrate_items, integrate_cull, then (live tiles << 32 | work items) and spares, %globaltimer nanoseconds, written by the kernels themselves
     b2r::Scratch trace;
     int trace_cap = 0, trace_n = 0;
     bool trace_on = false;
@@ -133,7 +140,7 @@ __device__ __forceinline__ void trace_begin(unsigned long long* tr) { if (tr) at
 __device__ __forceinline__ void trace_end(unsigned long long* tr) { if (tr) atomicMax(tr + 1, gtimer_ns()); }
 static inline unsigned long long* trace_row(b2r_ctx* ctx, int kernel) {
     if (!ctx->trace_on || ctx->trace_n >= ctx->trace_cap) return nullptr;
-    return (unsigned long long*)ctx->trace.ptr + (size_t)ctx->trace_n * 8 + kernel * 2;
+    return (unsigned long long*)ctx->trace.ptr + (size_t)ctx->trace_n * 16 + kernel * 2;
 }
 static inline cudaStream_t S(void* s) { return (cudaStream_t)s; }
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

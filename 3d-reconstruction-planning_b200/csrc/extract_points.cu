@@ -260,6 +260,7 @@ int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_poi
     const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
     *n_points = 0;
     ctx->pc_n = 0;
+    ctx->pc_vol = vol->d_tsdfw; ctx->pc_gen = ctx->write_gen;
     if (nz <= 0 || R < 3) return 0;
     const int64_t n = (int64_t)nz * R * R;
     const int nblocks = cdiv(n, PC_THREADS);
@@ -292,6 +293,8 @@ int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_poi
 static int points_emit(b2r_ctx* ctx, const b2r_volume* vol, int unit_res, const int32_t* unit_offset, const int32_t* d_unit_stamp,
                        double* d_points, double* d_normals, double* d_colors, void* stream) {
     B2R_CUDA(cudaSetDevice(ctx->device));
+    B2R_CHECK(ctx->pc_vol == vol->d_tsdfw && ctx->pc_gen == ctx->write_gen, -9,
+              "b2r_extract_points_emit: the volume was written (or another volume counted) since b2r_extract_points_count; count again");
     const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
     if (nz <= 0 || R < 3 || ctx->pc_n == 0) return 0;
     B2R_CHECK(d_points && d_normals, -1, "b2r_extract_points_emit: NULL output");

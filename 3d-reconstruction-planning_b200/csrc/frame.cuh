@@ -8,6 +8,7 @@ namespace b2r {
 constexpr int SMALL_DMAX = 0;          // uint32: bits of the frame's max depth
 constexpr int SMALL_ITEMS = 8;         // uint32: integrate work items planned for the frame
 constexpr int SMALL_NEXT = 9;          // uint32: next work item to hand out
+constexpr int SMALL_LIVE_TILES = 11;   // uint32: tiles that survived integrate_cull_kernel
 constexpr int SMALL_TICKET = 10;       // uint32: warps of the streaming kernel that have finished (result write-back)
 constexpr int SMALL_TOTAL64 = 128;     // uint64 index (byte 1024): scan totals
 constexpr int SMALL_TOTAL64_B = 129;

@@ -305,6 +305,7 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
     *n_vertices = 0; *n_triangles = 0;
     ctx->mc_nv = ctx->mc_nt = 0;
     ctx->mc_R = R; ctx->mc_zb = zb; ctx->mc_ze = ze;
+    ctx->mc_vol = vol->d_tsdfw; ctx->mc_gen = ctx->write_gen;
     if (nz <= 0 || R < 2) return 0;
     const size_t planes = (size_t)nz + B2R_PAD_LO + B2R_PAD_HI;
     const size_t nvox_pad = planes * R * R;
@@ -359,6 +360,8 @@ static int mc_state_ok(b2r_ctx* ctx, const b2r_volume* vol, const char* who) {
     B2R_CHECK(ctx && vol && vol->d_tsdfw, -1, "%s: NULL argument", who);
     B2R_CHECK(ctx->mc_R == vol->resolution && ctx->mc_zb == vol->z_begin && ctx->mc_ze == vol->z_end, -9,
               "%s: call b2r_extract_mesh_count on this volume first", who);
+    B2R_CHECK(ctx->mc_vol == vol->d_tsdfw && ctx->mc_gen == ctx->write_gen, -9,
+              "%s: the volume was written (or another volume counted) since b2r_extract_mesh_count; count again", who);
     return 0;
 }
 

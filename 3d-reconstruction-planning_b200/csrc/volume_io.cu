@@ -82,6 +82,7 @@ int b2r_volume_export(b2r_ctx* ctx, const b2r_volume* vol, float* d_tsdf_out, fl
 int b2r_volume_import(b2r_ctx* ctx, const b2r_volume* vol, const float* d_tsdf_in, const float* d_weight_in,
                       const float* d_color_in, void* stream) {
     B2R_CHECK(ctx && vol && vol->d_tsdfw && d_tsdf_in && d_weight_in, -1, "b2r_volume_import: NULL argument");
+    ctx->write_gen++;
     B2R_CUDA(cudaSetDevice(ctx->device));
     B2R_CUDA(join_side(ctx, S(stream)));   // items kernels of earlier integrate calls run on the side stream
     const int nz = vol->z_end - vol->z_begin, R = vol->resolution;

@@ -85,8 +85,9 @@ int b2r_ctx_kernel_time(b2r_ctx* ctx, double* ms_total, int64_t* n_launches);
 /* Device-side timeline of the integrate calls (tuning / profiles/ evidence; the kernels write %globaltimer
  * themselves, nothing is added to the streams).  b2r_ctx_trace(ctx, max_calls > 0) starts recording the next
  * max_calls b2r_integrate* calls (blocking: synchronises the device), max_calls = 0 stops.  b2r_ctx_trace_read
- * (blocking) copies, per recorded call, 8 uint64 nanosecond stamps: {start, end} of frame_prepare_kernel,
- * integrate_plan_kernel, integrate_items_kernel, and two spare zeros (0 = kernel did not run). */
+ * (blocking) copies, per recorded call, 16 uint64: nanosecond stamps {start, end} of frame_prepare_kernel,
+ * integrate_plan_kernel, integrate_items_kernel, integrate_cull_kernel (0 = kernel did not run), then
+ * (tiles that survived the cull << 32 | work items of the frame) and 7 spare zeros. */
 int b2r_ctx_trace(b2r_ctx* ctx, int max_calls);
 int b2r_ctx_trace_read(b2r_ctx* ctx, unsigned long long* out, int cap_calls, int* n_calls);
 

@@ -1,0 +1,9 @@
+#!/bin/bash
+# gpu_retry.sh <timeout_s> <command...>: gpurun with retries while the pod answers "busy / draining" (nothing charged).
+T=$1; shift
+for i in $(seq 1 40); do
+  out=$(/usr/local/graft/bin/gpurun --timeout $T -- "$@" 2>&1)
+  if echo "$out" | grep -q "status=transient\|status=busy\|nothing was charged"; then sleep 45; continue; fi
+  echo "$out"; exit 0
+done
+echo "$out"; exit 3

@@ -50,7 +50,8 @@ for a, b in zip(cuts[:-1], cuts[1:]):
     t_issue = time.perf_counter() - t0
     ctx.sync()
     t_all = time.perf_counter() - t0
-    tr = ctx.trace_read().astype(np.float64) / 1000.0
+    tr, n_live, n_items = ctx.trace_read()
+    tr = tr.astype(np.float64) / 1000.0
     ctx.trace(0)
     dur = tr[:, :, 1] - tr[:, :, 0]
     st = tr[:, 2, 0]
@@ -61,12 +62,14 @@ for a, b in zip(cuts[:-1], cuts[1:]):
 
     def q(x):
         return "%6.1f [%5.1f %5.1f]" % (np.median(x), np.percentile(x, 10), np.percentile(x, 90))
-    print("[%4d,%4d) prepare %s  plan %s  items %s  step %s  gap %s  plan_end->items_start %s  host issue %.1f us/call, wall %.1f us/call"
-          % (a, b, q(dur[:, 0]), q(dur[:, 1]), q(dur[:, 2]), q(step), q(gap), q(slack), 1e6 * t_issue / len(frames), 1e6 * t_all / len(frames)))
+    print("[%4d,%4d) prepare %s  cull %s  plan %s  items %s  step %s  gap %s  plan_end->items_start %s  live tiles %d items %d  host issue %.1f us/call, wall %.1f us/call"
+          % (a, b, q(dur[:, 0]), q(dur[:, 3]), q(dur[:, 1]), q(dur[:, 2]), q(step), q(gap), q(slack), np.median(n_live), np.median(n_items),
+             1e6 * t_issue / len(frames), 1e6 * t_all / len(frames)))
     if os.environ.get("DUMP"):
         base = tr[0, 0, 0]
         for i in range(min(len(tr), int(os.environ["DUMP"]))):
-            print("  frame %2d  prepare %7.1f-%7.1f  plan %7.1f-%7.1f  items %7.1f-%7.1f" % (
-                i, tr[i, 0, 0] - base, tr[i, 0, 1] - base, tr[i, 1, 0] - base, tr[i, 1, 1] - base, tr[i, 2, 0] - base, tr[i, 2, 1] - base))
+            print("  frame %2d  prepare %7.1f-%7.1f  cull %7.1f-%7.1f  plan %7.1f-%7.1f  items %7.1f-%7.1f" % (
+                i, tr[i, 0, 0] - base, tr[i, 0, 1] - base, tr[i, 3, 0] - base, tr[i, 3, 1] - base, tr[i, 1, 0] - base, tr[i, 1, 1] - base,
+                tr[i, 2, 0] - base, tr[i, 2, 1] - base))
     del v
     torch.cuda.empty_cache()
