@@ -73,6 +73,7 @@ SIGNATURES = {
     "b2r_integrate_units": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, C.POINTER(Intrinsic), c_dp, c_dp, C.c_int, C.c_int,
                                       C.POINTER(C.c_int32), c_vp, C.c_int32, c_vp, c_vp, c_vp, c_vp]),
     "b2r_selftest_div": (C.c_int, [c_vp, C.c_int64, C.c_uint32, c_i64p, c_vp]),
+    "b2r_selftest_chain": (C.c_int, [c_vp, C.c_int64, C.c_uint32, c_i64p, c_vp]),
     "b2r_volume_reset": (C.c_int, [c_vp, C.POINTER(Volume), c_vp]),
     "b2r_volume_export": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, c_vp, c_vp]),
     "b2r_volume_import": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, c_vp, c_vp]),

@@ -43,7 +43,15 @@ int b2r_ctx_create(int device, b2r_ctx** out) {
         const char* e2 = getenv("B2R_ASYNC");
         c->async_items = !(e2 && e2[0] == '0');
     }
-    B2R_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+    {
+        // The streaming kernels' stream gets the highest priority: when a streaming kernel ends, the next one (same
+        // stream) and the preparation of the frame after it (caller's stream, waiting for the same frame slot) become
+        // ready together, and whichever the hardware picks first delays the other -- with equal priorities it was the
+        // preparation every other frame: 8.5 us between consecutive streaming kernels instead of 3.8 (timeline probe).
+        int lo = 0, hi = 0;
+        B2R_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        B2R_CUDA(cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, hi));
+    }
     B2R_CUDA(cudaStreamCreateWithFlags(&c->copy, cudaStreamNonBlocking));
     for (auto& f : c->fslot) {
         B2R_CUDA(cudaEventCreateWithFlags(&f.ev_plan, cudaEventDisableTiming));

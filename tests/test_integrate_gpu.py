@@ -155,3 +155,17 @@ def test_shared_reciprocal_division_is_ieee(o3d):
         bad = (C.c_int64 * 4)(-1, -1, -1, -1)
         _lib.check(_lib.load().b2r_selftest_div(c.handle, 1 << 28, seed, bad, c.stream()))
         assert list(bad) == [0, 0, 0, 0], list(bad)
+
+
+def test_chain_jump_equals_stepped_chain(o3d):
+    """chain_jump (a measured-and-shelved alternative to walking the planes below a z-slab, csrc/tsdf_integrate.cu)
+    reaches a slab's first plane by mantissa arithmetic instead of walking Open3D's float32 adds; on the
+    device the result must equal the stepped chain bit for bit (2^22 cases per seed: camera-like magnitudes, zero
+    crossings, exact ties, binade edges, denormals / huge steps, increments below half an ulp)."""
+    import ctypes as C
+    from b200recon import _lib, runtime
+    c = runtime.ctx()
+    for seed in (3, 987654321):
+        bad = C.c_int64(-1)
+        _lib.check(_lib.load().b2r_selftest_chain(c.handle, 1 << 22, seed, C.byref(bad), c.stream()))
+        assert bad.value == 0, bad.value
