@@ -353,22 +353,29 @@ def run_gpu(args):
         # (mean over the ranks -- which also halves the noise), or the slabs would not tile the cube
         work = parallel.agree_plane_work(work, device=dev)
         ranges = parallel.balanced_slab_ranges(work, world)
-        # one feedback step (the kernel times repeat to about +-5 %, more steps chase noise): time the streaming kernel of every rank on its slab over 12 frames, rescale the work
-        # estimate of each slab to its measured time, cut again (setup, outside the timed region; one all_gather of a float)
-        for _ in range(1):
+        # three feedback steps on what the bench measures -- the time per frame of every rank on its slab (64 frames,
+        # CUDA events around the loop; NOT the streaming kernel alone: for the first and last slab, which hold most of
+        # the cube's planes, planning is a larger share of the frame than for the thin middle slabs): rescale the work
+        # estimate of each slab to its measured time, cut again (setup, outside the timed region; one all_reduce of
+        # world floats per step)
+        for _ in range(3):
             zb, ze = ranges[rank]
             v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
                                                             syn.volume_origin(L), z_range=(zb, ze), device=local)
             v.count_updates = False
             for k in range(3):
                 v.integrate_device(depth_f[k % nf], rgb[k % nf], intr, exts[k % nf])
-            ctx.kernel_timing(True)
-            for k in range(0, nf, max(1, nf // 12)):
+            ctx.sync()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record()
+            ks = list(range(0, nf, max(1, nf // 64)))
+            for k in ks:
                 v.integrate_device(depth_f[k], rgb[k], intr, exts[k])
-            ctx.kernel_timing(False)
-            t_ms, t_n = ctx.kernel_time()
+            ctx.join()
+            f1.record()
+            torch.cuda.synchronize()
             tt = torch.zeros(world, dtype=torch.float64, device=dev)
-            tt[rank] = t_ms / max(t_n, 1)
+            tt[rank] = f0.elapsed_time(f1) / len(ks)
             dist.all_reduce(tt)
             ranges = parallel.rebalance_slab_ranges(ranges, work, tt.cpu().numpy())
             del v
@@ -445,7 +452,12 @@ def run_gpu(args):
         upd = vol.updates() - upd0
         timed.local_updates = upd          # this rank's own share (roofline of rank 0's kernel)
         launches = ctx.launch_count() - l0
+        timed.rank_ms = [ms]
         if world > 1:
+            tr_ = torch.zeros(world, dtype=torch.float64, device=dev)
+            tr_[rank] = ms
+            dist.all_reduce(tr_)
+            timed.rank_ms = [float(x) for x in tr_.cpu()]
             t = torch.tensor([ms], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
@@ -455,6 +467,7 @@ def run_gpu(args):
         return ms, upd, launches
 
     ms, _, launches = timed(step_dev, args.steps, args.warmup)
+    rank_ms_per_step = [round(x / args.steps, 5) for x in timed.rank_ms]
     # dominant kernel alone: CUDA events (on the stream it is launched on) around every integrate_items launch
     # of the same steps, run again
     ctx.kernel_timing(True)
@@ -531,7 +544,7 @@ def run_gpu(args):
             "metric": "TSDF integration frames/s (%dx%d RGB-D into dense TSDF+colour volume)" % (K["width"], K["height"]),
             "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
+            "dtype": "f32", "data": "synthetic", "rank_ms_per_step": rank_ms_per_step,
             "config": {"workload": args.workload, "resolution": R, "voxel_mm": 1000.0 * L / R, "frames_in_orbit": len(poses),
                        "frame": "%dx%d uint16 depth + uint8 rgb" % (K["width"], K["height"]), "sharding": "z-slab x%d" % world, "slab_boundaries": [a for a, _ in ranges] + [R],
                        "l2": "volume (%.1f GB) >> L2; consecutive frames touch overlapping voxels as in a real "
@@ -552,7 +565,7 @@ def run_gpu(args):
                                 "(convert_rgb_to_intensity=False) -> vol.integrate(rgbd, intrinsic, extrinsic)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src,
-                         "kernel": "integrate_items_kernel", "peak_source": peak_src,
+                         "kernel": "integrate_tiles_kernel (rank 0's slab: plan + stream fused)" if (ze - zb) <= 96 else "integrate_items_kernel", "peak_source": peak_src,
                          "kernel_ms_per_launch": k_ms_timed / max(args.steps, 1),
                          "alg_bytes_per_launch": alg_bytes, "bytes_per_update": B_UPD,
                          "frac_of_nominal_8TBs": achieved / 8000.0,
