@@ -1,19 +1,27 @@
 // Batched ICP -- replaces Open3D pipelines::registration::RegistrationICP (stitcher.py:94-110; the
 // north_star variant is TransformationEstimationPointToPlane; arithmetic in SURVEY.md A.5).
 //
-// Per pair, once:   voxel-hash of the target (open-addressing table keyed by the 3x21-bit cell
-//                   coordinate, counting sort of the points by cell: count -> scan -> scatter).
-// Per iteration:    ONE kernel.  Each thread transforms its source points by the pair's current T
-//                   (float64), finds the exact nearest target point within the radius (strict
-//                   d^2 < r^2, ties -> lowest target index) by walking the hash cells ring by ring
-//                   with box-distance pruning, and accumulates count, sum d^2 and the 27 normal-equation
-//                   terms (21 upper J^T J + 6 J^T r for point-to-plane; centroid / cross-covariance sums
-//                   for point-to-point) in float64.  Partials are reduced with warp shuffles, one
-//                   shared-memory pass per block and ONE atomic ticket per block; the last block of the
-//                   pair sums the block partials in a fixed order (deterministic), evaluates Open3D's
-//                   convergence test against the previous iteration, solves the 6x6 system (LDL^T with
-//                   diagonal pivoting) or the 3x3 SVD (Umeyama), and composes T <- update * T -- on the
-//                   device, so the max_iteration+1 launches run back to back with no host sync.
+// Per pair, once:   a DENSE uniform grid over the target's bounding box (cell ~2.5 point spacings, at least r/16; one
+//                   uint32 per cell = the end of the cell's run in the cell-sorted point array, so cell c is
+//                   [E[c-1], E[c]) and a row of consecutive x cells is ONE contiguous run): count -> scan -> scatter.
+//                   With 180 GB of HBM a few million cells per pair cost nothing, and a cell lookup is two adjacent
+//                   loads instead of a 64-bit hash and a probe chain (round 1's open-addressing table).
+// Per iteration:    TWO kernels.
+//   icp_search_kernel      a thread per source point, small register footprint (occupancy hides the L2 latency): transform
+//                          by the pair's current T (float64), walk the grid ring by ring around the query's cell -- every
+//                          (dy, dz) row of a ring is one run of candidates, rows / end cells farther than the best
+//                          distance so far are skipped from per-query face distances, the walk stops when the next ring
+//                          cannot hold a closer point -- exact nearest target point within the radius (strict d^2 < r^2,
+//                          ties -> lowest target index); writes the hit position and d^2.
+//   icp_accumulate_kernel  a thread per 8 source points with room for the 29 float64 sums in registers (round 1's single
+//                          kernel was capped at 40 registers for the search and spilled 4.9 KB per thread here): count,
+//                          sum d^2 and the 27 normal-equation terms (21 upper J^T J + 6 J^T r for point-to-plane; centroid
+//                          / cross-covariance sums for point-to-point; two residuals per correspondence for colored ICP),
+//                          warp shuffles -> one shared-memory pass -> ONE atomic ticket per block; the last block of the
+//                          pair sums the block partials in a fixed order (deterministic), evaluates Open3D's convergence
+//                          test, solves the 6x6 system (LDL^T with diagonal pivoting) or the 3x3 SVD (Umeyama) and composes
+//                          T <- update * T -- on the device, so the 2 (max_iteration + 1) launches run back to back with
+//                          no host sync.
 // Pairs are independent (blockIdx.y), so a batch fills the GPU; batches are distributed round-robin
 // over GPUs by the host with no collective.
 #include "frame.cuh"
@@ -21,19 +29,17 @@
 
 namespace b2r {
 
-#ifndef B2R_ICP_MINB
-#define B2R_ICP_MINB 6
-#endif
 constexpr int ICP_THREADS = 256;
-constexpr int ICP_PTS_PER_THREAD = 4;
+constexpr int ICP_ACC_PTS = 8;     // source points per thread of the accumulate kernel
 constexpr int ICP_NACC = 29;       // [0] count, [1] sum d^2, [2..28] estimation sums
-constexpr int ICP_MAX_RINGS = 4;   // cell size h >= r / ICP_MAX_RINGS
-constexpr unsigned long long EMPTY_KEY = 0xffffffffffffffffull;
+constexpr int ICP_MAX_RINGS = 16;  // cell size h >= r / ICP_MAX_RINGS (empty cells of the dense grid are cheap to skip)
+constexpr long long ICP_MAX_CELLS = 1ll << 25;   // per pair (128 MB of uint32); coarser cells beyond that
 
 struct IcpPair {
-    long long src_off, n_src, tgt_off, n_tgt, tab_off;
-    unsigned int tab_mask;     // table size - 1 (power of two)
-    int n_blocks;
+    long long src_off, n_src, tgt_off, n_tgt;
+    long long cell_off;        // first cell of this pair in the batch's cell array
+    int nx, ny, nz;            // grid dimensions (x fastest)
+    int n_blocks;              // blocks of the accumulate kernel that hold points of this pair
     int rings;                 // K = ceil(r / h)
     double gmin[3];            // grid origin
     double h, inv_h;
@@ -92,78 +98,69 @@ __global__ void __launch_bounds__(256) icp_bbox_kernel(const double* __restrict_
     }
 }
 
-// one thread per pair: choose the cell size from the radius and the point density
-__global__ void icp_setup_kernel(IcpPair* __restrict__ pairs, const long long* __restrict__ bb, int n_pairs, double r) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n_pairs) return;
-    IcpPair& P = pairs[p];
+// Host side of the grid setup: cell size from the radius and the point density, dimensions from the bounding box.
+#ifndef B2R_ICP_CELL_SPACINGS
+#define B2R_ICP_CELL_SPACINGS 2.5
+#endif
+static void icp_grid_setup(IcpPair& P, const double* bmin, const double* bmax, double r) {
     double e[3];
     for (int k = 0; k < 3; ++k) {
-        P.bmin[k] = P.n_tgt > 0 ? dec_double(bb[p * 6 + k]) : 0.0;
-        P.bmax[k] = P.n_tgt > 0 ? dec_double(bb[p * 6 + 3 + k]) : 0.0;
+        P.bmin[k] = P.n_tgt > 0 ? bmin[k] : 0.0;
+        P.bmax[k] = P.n_tgt > 0 ? bmax[k] : 0.0;
         e[k] = P.bmax[k] - P.bmin[k];
     }
     // surface-like clouds: mean spacing ~ sqrt(largest bbox face / N)
     const double a = fmax(e[0] * e[1], fmax(e[1] * e[2], e[0] * e[2]));
     const double spacing = sqrt(fmax(a, 1e-300) / (double)(P.n_tgt > 0 ? P.n_tgt : 1));
-    double h = fmax(2.5 * spacing, r / (double)ICP_MAX_RINGS);
+    double h = fmax(B2R_ICP_CELL_SPACINGS * spacing, r / (double)ICP_MAX_RINGS);
     if (h > r) h = r;
-    // keep cell coordinates inside 21 bits
-    const double emax = fmax(e[0], fmax(e[1], e[2])) + 2.0 * (r + h);
-    if (emax / h > 2000000.0) h = emax / 2000000.0;
+    if (!(h > 0.0)) h = r;
+    for (;;) {      // the grid covers the bounding box plus one cell on every side
+        double cells = 1.0;
+        for (int k = 0; k < 3; ++k) cells *= floor(e[k] / h) + 3.0;
+        if (cells <= (double)ICP_MAX_CELLS) break;
+        h *= 1.25;
+    }
     P.h = h;
     P.inv_h = 1.0 / h;
     P.rings = (int)ceil(r / h - 1e-12);
     if (P.rings < 1) P.rings = 1;
-    for (int k = 0; k < 3; ++k) P.gmin[k] = P.bmin[k] - (r + 2.0 * h);
+    for (int k = 0; k < 3; ++k) P.gmin[k] = P.bmin[k] - h;
+    P.nx = (int)floor(e[0] / h) + 3; P.ny = (int)floor(e[1] / h) + 3; P.nz = (int)floor(e[2] / h) + 3;
 }
 
-__device__ __forceinline__ unsigned long long cell_key(int ix, int iy, int iz) {
-    return ((unsigned long long)(unsigned)ix << 42) | ((unsigned long long)(unsigned)iy << 21) | (unsigned long long)(unsigned)iz;
-}
-__device__ __forceinline__ unsigned int hash_key(unsigned long long k) {
-    k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
-    return (unsigned int)k;
+// cell of a target point (inside the grid by construction; clamped against rounding at the box faces)
+__device__ __forceinline__ uint32_t icp_cell_of(const IcpPair& P, const double* q) {
+    int ix = (int)floor((q[0] - P.gmin[0]) * P.inv_h), iy = (int)floor((q[1] - P.gmin[1]) * P.inv_h),
+        iz = (int)floor((q[2] - P.gmin[2]) * P.inv_h);
+    ix = min(max(ix, 0), P.nx - 1); iy = min(max(iy, 0), P.ny - 1); iz = min(max(iz, 0), P.nz - 1);
+    return (uint32_t)((iz * P.ny + iy) * P.nx + ix);
 }
 
-// insert every target point's cell; remember the slot; count points per slot
-__global__ void __launch_bounds__(256) icp_hash_insert_kernel(const double* __restrict__ tgt,
-                                                              const IcpPair* __restrict__ pairs,
-                                                              unsigned long long* __restrict__ keys,
-                                                              uint32_t* __restrict__ counts,
-                                                              uint32_t* __restrict__ slot_of) {
+// count the target points per cell; remember each point's cell
+__global__ void __launch_bounds__(256) icp_cell_count_kernel(const double* __restrict__ tgt, const IcpPair* __restrict__ pairs,
+                                                             uint32_t* __restrict__ cells, uint32_t* __restrict__ cell_of) {
     const IcpPair P = pairs[blockIdx.y];
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n_tgt) return;
-    const double* q = tgt + (P.tgt_off + i) * 3;
-    const int ix = (int)floor((q[0] - P.gmin[0]) * P.inv_h), iy = (int)floor((q[1] - P.gmin[1]) * P.inv_h),
-              iz = (int)floor((q[2] - P.gmin[2]) * P.inv_h);
-    const unsigned long long key = cell_key(ix, iy, iz);
-    unsigned int s = hash_key(key) & P.tab_mask;
-    while (true) {
-        const unsigned long long prev = atomicCAS(&keys[P.tab_off + s], EMPTY_KEY, key);
-        if (prev == EMPTY_KEY || prev == key) break;
-        s = (s + 1) & P.tab_mask;
-    }
-    atomicAdd(&counts[P.tab_off + s], 1u);
-    slot_of[P.tgt_off + i] = s;
+    const uint32_t c = icp_cell_of(P, tgt + (P.tgt_off + i) * 3);
+    atomicAdd(&cells[P.cell_off + c], 1u);
+    cell_of[P.tgt_off + i] = c;
 }
 
-// counting-sort scatter: sorted position = start[slot] + cursor++
-__global__ void __launch_bounds__(256) icp_hash_scatter_kernel(const double* __restrict__ tgt,
-                                                               const double* __restrict__ nrm,
-                                                               const IcpPair* __restrict__ pairs,
-                                                               const uint32_t* __restrict__ starts,
-                                                               uint32_t* __restrict__ cursor,
-                                                               const uint32_t* __restrict__ slot_of,
+// counting-sort scatter.  `cells` holds the exclusive scan of the counts (= every cell's start in the batch-wide sorted
+// array) on entry; each point takes the next position of its cell, which leaves the cell's END in `cells` -- the form
+// the search reads: cell c = [cells[c - 1], cells[c]), a run of consecutive cells = [cells[first - 1], cells[last]).
+__global__ void __launch_bounds__(256) icp_cell_scatter_kernel(const double* __restrict__ tgt, const double* __restrict__ nrm,
+                                                               const IcpPair* __restrict__ pairs, uint32_t* __restrict__ cells,
+                                                               const uint32_t* __restrict__ cell_of,
                                                                double* __restrict__ s_pts, double* __restrict__ s_nrm,
                                                                int32_t* __restrict__ s_idx) {
     const IcpPair P = pairs[blockIdx.y];
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n_tgt) return;
     const long long g = P.tgt_off + i;
-    const unsigned int s = slot_of[g];
-    const uint32_t pos = starts[P.tab_off + s] + atomicAdd(&cursor[P.tab_off + s], 1u);  // global sorted index
+    const uint32_t pos = atomicAdd(&cells[P.cell_off + cell_of[g]], 1u);      // batch-wide sorted index
 #pragma unroll
     for (int k = 0; k < 3; ++k) s_pts[(long long)pos * 3 + k] = tgt[g * 3 + k];
     if (nrm && s_nrm) {
@@ -344,9 +341,9 @@ struct IcpArgs {
     const double* s_pts;
     const double* s_nrm;
     const int32_t* s_idx;
-    const unsigned long long* keys;
-    const uint32_t* starts;
-    const uint32_t* counts;
+    const uint32_t* cells;     // per cell: END of its run in the sorted arrays (cells[-1] = 0 exists)
+    int32_t* hit;              // per source point: sorted position of its correspondence, -1 = none
+    double* hit_d2;            // and the squared distance
     const IcpPair* pairs;
     IcpState* states;
     double* partials;      // [pair][block][ICP_NACC]
@@ -377,8 +374,114 @@ __global__ void __launch_bounds__(256) icp_gather_color_kernel(const double* __r
     for (int k = 0; k < 3; ++k) s_grad[pos * 3 + k] = tgt_grad[g * 3 + k];
 }
 
+// distance along one axis from the query to the cells `o` cells away from its own (em / ep: distance to the lower /
+// upper face of its own cell)
+__device__ __forceinline__ double icp_axis_dist(int o, double em, double ep, double h) {
+    return o == 0 ? 0.0 : (o < 0 ? (double)(-o - 1) * h + em : (double)(o - 1) * h + ep);
+}
+
+// candidates [m0, m1) of one run against the query: exact float64 distances, strict <, ties -> lowest target index
+__device__ __forceinline__ void icp_scan_run(const IcpArgs& A, uint32_t m0, uint32_t m1, double q0, double q1, double q2,
+                                             double& best, int& bestpos, int& bestj) {
+    for (uint32_t m = m0; m < m1; ++m) {
+        const double tx = __ldg(&A.s_pts[(long long)m * 3]) - q0;
+        const double ty = __ldg(&A.s_pts[(long long)m * 3 + 1]) - q1;
+        const double tz = __ldg(&A.s_pts[(long long)m * 3 + 2]) - q2;
+        const double d2 = tx * tx + ty * ty + tz * tz;
+        if (d2 < best) { best = d2; bestpos = (int)m; bestj = __ldg(&A.s_idx[m]); }
+        else if (d2 == best && bestpos >= 0) {
+            const int j = __ldg(&A.s_idx[m]);
+            if (j < bestj) { bestpos = (int)m; bestj = j; }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid_constant__ IcpArgs A) {
+    const int p = blockIdx.y;
+    const IcpState& St = A.states[p];
+    if (St.done) return;
+    const IcpPair& P = A.pairs[p];
+    const long long i = (long long)blockIdx.x * ICP_THREADS + threadIdx.x;
+    if (i >= P.n_src) return;
+    const double* s = A.src + (P.src_off + i) * 3;
+    const double sx = s[0], sy = s[1], sz = s[2];
+    const double q0 = St.T[0] * sx + St.T[1] * sy + St.T[2] * sz + St.T[3];
+    const double q1 = St.T[4] * sx + St.T[5] * sy + St.T[6] * sz + St.T[7];
+    const double q2 = St.T[8] * sx + St.T[9] * sy + St.T[10] * sz + St.T[11];
+    double best = A.r2;
+    int bestpos = -1;
+    int bestj = 0x7fffffff;
+    // reject queries farther than r from the target's bounding box
+    double bd = 0.0;
+    {
+        const double qq[3] = {q0, q1, q2};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double d = qq[k] < P.bmin[k] ? P.bmin[k] - qq[k] : (qq[k] > P.bmax[k] ? qq[k] - P.bmax[k] : 0.0);
+            bd += d * d;
+        }
+    }
+    if (bd < A.r2 && P.n_tgt > 0) {
+        const double h = P.h;
+        const double g0 = (q0 - P.gmin[0]) * P.inv_h, g1 = (q1 - P.gmin[1]) * P.inv_h, g2 = (q2 - P.gmin[2]) * P.inv_h;
+        const double fl0 = floor(g0), fl1 = floor(g1), fl2 = floor(g2);
+        const int c0 = (int)fl0, c1 = (int)fl1, c2 = (int)fl2;       // may lie outside the grid (within r of the box)
+        const double em0 = (g0 - fl0) * h, ep0 = h - em0, em1 = (g1 - fl1) * h, ep1 = h - em1, em2 = (g2 - fl2) * h, ep2 = h - em2;
+        const double face = fmin(fmin(fmin(em0, ep0), fmin(em1, ep1)), fmin(em2, ep2));
+        const int nx = P.nx, ny = P.ny, nz = P.nz;
+        const uint32_t* E = A.cells + P.cell_off;
+        for (int ring = 0; ring <= P.rings + 1; ++ring) {
+            if (ring > 0) {
+                const double lo = (double)(ring - 1) * h + face;   // everything in ring >= `ring` is at least this far
+                if (lo * lo >= best) break;
+            }
+            for (int dz = -ring; dz <= ring; ++dz) {
+                const int cz = c2 + dz;
+                if ((unsigned)cz >= (unsigned)nz) continue;
+                const double ez = icp_axis_dist(dz, em2, ep2, h);
+                for (int dy = -ring; dy <= ring; ++dy) {
+                    const int cy = c1 + dy;
+                    if ((unsigned)cy >= (unsigned)ny) continue;
+                    const double ey = icp_axis_dist(dy, em1, ep1, h);
+                    const double row2 = ey * ey + ez * ez;
+                    // slack of a few ulps: the cell of a point was computed with rounded arithmetic
+                    if (row2 > best * (1.0 + 1e-9) + 1e-24) continue;
+                    const uint32_t* row = E + ((long long)cz * ny + cy) * nx;
+                    const bool shell = (dz == -ring || dz == ring || dy == -ring || dy == ring);
+                    // a shell row (and ring 0) is ONE run of x cells; an inner row contributes its two end cells
+                    const int nseg = (shell || ring == 0) ? 1 : 2;
+                    for (int sg = 0; sg < nseg; ++sg) {
+                        int xa, xb;
+                        if (nseg == 1) { xa = -ring; xb = ring; }
+                        else { xa = xb = (sg == 0 ? -ring : ring); }
+                        // trim cells whose box is farther than the best distance so far from both ends of the run
+                        const double thr = best * (1.0 + 1e-9) + 1e-24 - row2;
+                        while (xa <= xb) {
+                            const double ex = icp_axis_dist(xa, em0, ep0, h);
+                            if (ex * ex <= thr) break;
+                            ++xa;
+                        }
+                        while (xb >= xa) {
+                            const double ex = icp_axis_dist(xb, em0, ep0, h);
+                            if (ex * ex <= thr) break;
+                            --xb;
+                        }
+                        xa = max(xa + c0, 0);
+                        xb = min(xb + c0, nx - 1);
+                        if (xa > xb) continue;
+                        icp_scan_run(A, __ldg(row + xa - 1), __ldg(row + xb), q0, q1, q2, best, bestpos, bestj);
+                    }
+                }
+            }
+        }
+    }
+    if (A.corr) A.corr[P.src_off + i] = bestpos >= 0 ? bestj : -1;
+    A.hit[P.src_off + i] = bestpos;
+    A.hit_d2[P.src_off + i] = best;
+}
+
 template <int EST>
-__global__ void __launch_bounds__(ICP_THREADS, B2R_ICP_MINB) icp_iterate_kernel(const __grid_constant__ IcpArgs A) {
+__global__ void __launch_bounds__(ICP_THREADS, 2) icp_accumulate_kernel(const __grid_constant__ IcpArgs A) {
     const int p = blockIdx.y;
     IcpState& St = A.states[p];
     if (St.done) return;
@@ -389,96 +492,18 @@ __global__ void __launch_bounds__(ICP_THREADS, B2R_ICP_MINB) icp_iterate_kernel(
     double T[12];
 #pragma unroll
     for (int i = 0; i < 12; ++i) T[i] = St.T[i];
-
-    // Two phases per thread: (1) nearest-neighbour search for its ICP_PTS_PER_THREAD points, keeping only the hit
-    // position and squared distance; (2) accumulation.  The 29 float64 accumulators (58 registers) are not live
-    // during the latency-bound search, which is what sets the register count and with it the occupancy.
-    long long hit[ICP_PTS_PER_THREAD];
-    double hit_d2[ICP_PTS_PER_THREAD];
-    const long long base = (long long)blockIdx.x * (ICP_THREADS * ICP_PTS_PER_THREAD);
-#pragma unroll 1
-    for (int it = 0; it < ICP_PTS_PER_THREAD; ++it) {
-        hit[it] = -1; hit_d2[it] = 0.0;
-        const long long i = base + (long long)it * ICP_THREADS + threadIdx.x;
-        if (i >= P.n_src) continue;
-        const double* s = A.src + (P.src_off + i) * 3;
-        const double sx = s[0], sy = s[1], sz = s[2];
-        const double q[3] = {T[0] * sx + T[1] * sy + T[2] * sz + T[3], T[4] * sx + T[5] * sy + T[6] * sz + T[7],
-                             T[8] * sx + T[9] * sy + T[10] * sz + T[11]};
-        double best = A.r2;
-        long long bestpos = -1;
-        int bestj = 0x7fffffff;
-        // reject queries farther than r from the target's bounding box
-        double bd = 0.0;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const double d = q[k] < P.bmin[k] ? P.bmin[k] - q[k] : (q[k] > P.bmax[k] ? q[k] - P.bmax[k] : 0.0);
-            bd += d * d;
-        }
-        if (bd < A.r2 && P.n_tgt > 0) {
-            const double g[3] = {(q[0] - P.gmin[0]) * P.inv_h, (q[1] - P.gmin[1]) * P.inv_h, (q[2] - P.gmin[2]) * P.inv_h};
-            const int c[3] = {(int)floor(g[0]), (int)floor(g[1]), (int)floor(g[2])};
-            // distance from q to the nearest face of its own cell
-            double face = 1e300;
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const double f = g[k] - (double)c[k];
-                face = fmin(face, fmin(f, 1.0 - f));
-            }
-            face *= P.h;
-            for (int ring = 0; ring <= P.rings; ++ring) {
-                if (ring > 0) {
-                    const double lo = (double)(ring - 1) * P.h + face;  // everything in ring >= `ring` is at least this far
-                    if (lo * lo >= best) break;
-                }
-                for (int dz = -ring; dz <= ring; ++dz)
-                    for (int dy = -ring; dy <= ring; ++dy) {
-                        const bool shell_yz = (dz == -ring || dz == ring || dy == -ring || dy == ring);
-                        const int step = (shell_yz || ring == 0) ? 1 : 2 * ring;
-                        for (int dx = -ring; dx <= ring; dx += step) {
-                            const int cx = c[0] + dx, cy = c[1] + dy, cz = c[2] + dz;
-                            if ((cx | cy | cz) < 0) continue;
-                            // box distance pruning
-                            const double lx = P.gmin[0] + (double)cx * P.h, ly = P.gmin[1] + (double)cy * P.h, lz = P.gmin[2] + (double)cz * P.h;
-                            const double ex = q[0] < lx ? lx - q[0] : (q[0] > lx + P.h ? q[0] - (lx + P.h) : 0.0);
-                            const double ey = q[1] < ly ? ly - q[1] : (q[1] > ly + P.h ? q[1] - (ly + P.h) : 0.0);
-                            const double ez = q[2] < lz ? lz - q[2] : (q[2] > lz + P.h ? q[2] - (lz + P.h) : 0.0);
-                            // slack of a few ulps: the cell of a point was computed with rounded arithmetic
-                            if (ex * ex + ey * ey + ez * ez > best * (1.0 + 1e-9) + 1e-24) continue;
-                            const unsigned long long key = cell_key(cx, cy, cz);
-                            unsigned int sl = hash_key(key) & P.tab_mask;
-                            unsigned long long kk;
-                            while ((kk = __ldg(&A.keys[P.tab_off + sl])) != key && kk != EMPTY_KEY) sl = (sl + 1) & P.tab_mask;
-                            if (kk != key) continue;
-                            const uint32_t st = __ldg(&A.starts[P.tab_off + sl]), cn = __ldg(&A.counts[P.tab_off + sl]);
-                            for (uint32_t m = st; m < st + cn; ++m) {
-                                const double tx = __ldg(&A.s_pts[(long long)m * 3]) - q[0];
-                                const double ty = __ldg(&A.s_pts[(long long)m * 3 + 1]) - q[1];
-                                const double tz = __ldg(&A.s_pts[(long long)m * 3 + 2]) - q[2];
-                                const double d2 = tx * tx + ty * ty + tz * tz;
-                                if (d2 < best) { best = d2; bestpos = m; bestj = __ldg(&A.s_idx[m]); }
-                                else if (d2 == best && bestpos >= 0) {
-                                    const int j = __ldg(&A.s_idx[m]);
-                                    if (j < bestj) { bestpos = m; bestj = j; }
-                                }
-                            }
-                        }
-                    }
-            }
-        }
-        if (A.corr) A.corr[P.src_off + i] = bestpos >= 0 ? bestj : -1;
-        hit[it] = bestpos; hit_d2[it] = best;
-    }
+    const long long base = (long long)blockIdx.x * (ICP_THREADS * ICP_ACC_PTS);
 
     double acc[ICP_NACC];
 #pragma unroll
     for (int i = 0; i < ICP_NACC; ++i) acc[i] = 0.0;
-#pragma unroll
-    for (int it = 0; it < ICP_PTS_PER_THREAD; ++it) {
-        const long long bestpos = hit[it];
-        if (bestpos < 0) continue;
-        const double best = hit_d2[it];
+#pragma unroll 2
+    for (int it = 0; it < ICP_ACC_PTS; ++it) {
         const long long i = base + (long long)it * ICP_THREADS + threadIdx.x;
+        if (i >= P.n_src) break;
+        const long long bestpos = (long long)A.hit[P.src_off + i];
+        if (bestpos < 0) continue;
+        const double best = A.hit_d2[P.src_off + i];
         const double* s = A.src + (P.src_off + i) * 3;
         const double sx = s[0], sy = s[1], sz = s[2];
         const double q[3] = {T[0] * sx + T[1] * sy + T[2] * sz + T[3], T[4] * sx + T[5] * sy + T[6] * sz + T[7],
@@ -662,27 +687,23 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
     // ---- host-side pair table ----
     std::vector<IcpPair> hp(n_pairs);
     std::vector<IcpState> hs(n_pairs);
-    long long tab_total = 0;
     int max_blocks = 1;
-    long long max_nt = 0;
+    long long max_nt = 0, max_ns = 0;
     for (int p = 0; p < n_pairs; ++p) {
         IcpPair& P = hp[p];
         memset(&P, 0, sizeof(P));
         P.src_off = h_src_off[p]; P.n_src = h_src_off[p + 1] - h_src_off[p];
         P.tgt_off = h_tgt_off[p]; P.n_tgt = h_tgt_off[p + 1] - h_tgt_off[p];
         B2R_CHECK(P.n_src >= 0 && P.n_tgt >= 0, -5, "b2r_icp_batch: offsets must be non-decreasing");
-        const unsigned int tsz = next_pow2((unsigned long long)P.n_tgt * 2 + 16);
-        P.tab_off = tab_total; P.tab_mask = tsz - 1;
-        tab_total += tsz;
-        P.n_blocks = (int)((P.n_src + ICP_THREADS * ICP_PTS_PER_THREAD - 1) / (ICP_THREADS * ICP_PTS_PER_THREAD));
+        P.n_blocks = (int)((P.n_src + ICP_THREADS * ICP_ACC_PTS - 1) / (ICP_THREADS * ICP_ACC_PTS));
         if (P.n_blocks < 1) P.n_blocks = 1;
         if (P.n_blocks > max_blocks) max_blocks = P.n_blocks;
         if (P.n_tgt > max_nt) max_nt = P.n_tgt;
+        if (P.n_src > max_ns) max_ns = P.n_src;
         IcpState& Sx = hs[p];
         memset(&Sx, 0, sizeof(Sx));
         for (int i = 0; i < 16; ++i) Sx.T[i] = h_init ? h_init[p * 16 + i] : ((i % 5 == 0) ? 1.0 : 0.0);
     }
-    B2R_CHECK(tab_total < (1ll << 32), -8, "b2r_icp_batch: hash tables too large");
 
     // ---- scratch carving ----
     auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
@@ -692,31 +713,20 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
     IcpPair* d_pairs = (IcpPair*)ctx->icp_a.ptr;
     IcpState* d_states = (IcpState*)((char*)ctx->icp_a.ptr + sz_pairs);
     long long* d_bb = (long long*)((char*)ctx->icp_a.ptr + sz_pairs + sz_states);
-    const size_t sz_keys = al(sizeof(unsigned long long) * tab_total), sz_u32 = al(sizeof(uint32_t) * tab_total);
-    if (ctx->icp_b.ensure(sz_keys + 3 * sz_u32)) return -102;
-    unsigned long long* d_keys = (unsigned long long*)ctx->icp_b.ptr;
-    uint32_t* d_counts = (uint32_t*)((char*)ctx->icp_b.ptr + sz_keys);
-    uint32_t* d_starts = (uint32_t*)((char*)ctx->icp_b.ptr + sz_keys + sz_u32);
-    uint32_t* d_cursor = (uint32_t*)((char*)ctx->icp_b.ptr + sz_keys + 2 * sz_u32);
     const size_t sz_pts = al(sizeof(double) * 3 * (size_t)Nt);
     if (ctx->icp_c.ensure(2 * sz_pts + al(sizeof(int32_t) * (size_t)Nt) + al(sizeof(uint32_t) * (size_t)Nt))) return -102;
     double* d_spts = (double*)ctx->icp_c.ptr;
     double* d_snrm = (double*)((char*)ctx->icp_c.ptr + sz_pts);
     int32_t* d_sidx = (int32_t*)((char*)ctx->icp_c.ptr + 2 * sz_pts);
-    uint32_t* d_slot = (uint32_t*)((char*)ctx->icp_c.ptr + 2 * sz_pts + al(sizeof(int32_t) * (size_t)Nt));
+    uint32_t* d_cellof = (uint32_t*)((char*)ctx->icp_c.ptr + 2 * sz_pts + al(sizeof(int32_t) * (size_t)Nt));
     if (ctx->icp_d.ensure(sizeof(double) * ICP_NACC * (size_t)max_blocks * n_pairs)) return -102;
     double* d_partials = (double*)ctx->icp_d.ptr;
+    if (ctx->icp_f.ensure(al(sizeof(int32_t) * (size_t)Ns) + al(sizeof(double) * (size_t)Ns) + 256)) return -102;
+    int32_t* d_hit = (int32_t*)ctx->icp_f.ptr;
+    double* d_hitd2 = (double*)((char*)ctx->icp_f.ptr + al(sizeof(int32_t) * (size_t)Ns));
 
+    // ---- bounding boxes -> grids (one host round trip: the grid sizes decide the allocation) ----
     B2R_CUDA(cudaMemcpyAsync(d_pairs, hp.data(), sizeof(IcpPair) * n_pairs, cudaMemcpyHostToDevice, st));
-    B2R_CUDA(cudaMemcpyAsync(d_states, hs.data(), sizeof(IcpState) * n_pairs, cudaMemcpyHostToDevice, st));
-    // the two host vectors die at return: make sure the copies are done before that (pageable memory
-    // copies are staged synchronously by the runtime, this sync is for clarity)
-    B2R_CUDA(cudaStreamSynchronize(st));
-    B2R_CUDA(cudaMemsetAsync(d_keys, 0xff, sizeof(unsigned long long) * tab_total, st));
-    B2R_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(uint32_t) * tab_total, st));
-    B2R_CUDA(cudaMemsetAsync(d_cursor, 0, sizeof(uint32_t) * tab_total, st));
-
-    // ---- build the target hashes ----
     icp_bbox_init_kernel<<<cdiv(n_pairs * 6, 128), 128, 0, st>>>(d_bb, n_pairs);
     B2R_LAUNCH_CHECK(ctx);
     if (max_nt > 0) {
@@ -724,15 +734,40 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
         icp_bbox_kernel<<<dim3(bx, n_pairs), 256, 0, st>>>(d_tgt_points, d_pairs, d_bb);
         B2R_LAUNCH_CHECK(ctx);
     }
-    icp_setup_kernel<<<cdiv(n_pairs, 64), 64, 0, st>>>(d_pairs, d_bb, n_pairs, params->max_correspondence_distance);
-    B2R_LAUNCH_CHECK(ctx);
+    std::vector<long long> hbb((size_t)n_pairs * 6);
+    B2R_CUDA(cudaMemcpyAsync(hbb.data(), d_bb, sizeof(long long) * 6 * n_pairs, cudaMemcpyDeviceToHost, st));
+    B2R_CUDA(cudaStreamSynchronize(st));
+    long long cell_total = 0;
+    for (int p = 0; p < n_pairs; ++p) {
+        double bmin[3], bmax[3];
+        for (int k = 0; k < 3; ++k) {
+            const long long lo = hbb[(size_t)p * 6 + k], hi = hbb[(size_t)p * 6 + 3 + k];
+            const long long dl = lo < 0 ? (lo ^ 0x7fffffffffffffffll) : lo, dh = hi < 0 ? (hi ^ 0x7fffffffffffffffll) : hi;
+            memcpy(&bmin[k], &dl, 8);
+            memcpy(&bmax[k], &dh, 8);
+        }
+        icp_grid_setup(hp[p], bmin, bmax, params->max_correspondence_distance);
+        hp[p].cell_off = cell_total;
+        cell_total += (long long)hp[p].nx * hp[p].ny * hp[p].nz;
+    }
+    B2R_CHECK(cell_total < (1ll << 33), -8, "b2r_icp_batch: grids too large (%lld cells)", cell_total);
+    if (ctx->icp_b.ensure(sizeof(uint32_t) * (size_t)(cell_total + 64))) return -102;
+    uint32_t* d_cells = (uint32_t*)ctx->icp_b.ptr + 32;       // d_cells[-1] = 0: the start of the very first cell
+    B2R_CUDA(cudaMemcpyAsync(d_pairs, hp.data(), sizeof(IcpPair) * n_pairs, cudaMemcpyHostToDevice, st));
+    B2R_CUDA(cudaMemcpyAsync(d_states, hs.data(), sizeof(IcpState) * n_pairs, cudaMemcpyHostToDevice, st));
+    // the host vectors die at return: make sure the copies are done before that (pageable memory
+    // copies are staged synchronously by the runtime, this sync is for clarity)
+    B2R_CUDA(cudaStreamSynchronize(st));
+    B2R_CUDA(cudaMemsetAsync(ctx->icp_b.ptr, 0, sizeof(uint32_t) * (size_t)(cell_total + 64), st));
+
+    // ---- build the target grids ----
     if (max_nt > 0) {
         dim3 grid(cdiv(max_nt, 256), n_pairs);
-        icp_hash_insert_kernel<<<grid, 256, 0, st>>>(d_tgt_points, d_pairs, d_keys, d_counts, d_slot);
+        icp_cell_count_kernel<<<grid, 256, 0, st>>>(d_tgt_points, d_pairs, d_cells, d_cellof);
         B2R_LAUNCH_CHECK(ctx);
-        if (int rc = scan_exclusive_u32(ctx, d_counts, d_starts, tab_total, nullptr, st)) return rc;
-        icp_hash_scatter_kernel<<<grid, 256, 0, st>>>(d_tgt_points, d_tgt_normals, d_pairs, d_starts, d_cursor, d_slot,
-                                                      d_spts, d_snrm, d_sidx);
+        if (int rc = scan_exclusive_u32(ctx, d_cells, d_cells, cell_total, nullptr, st)) return rc;
+        icp_cell_scatter_kernel<<<grid, 256, 0, st>>>(d_tgt_points, d_tgt_normals, d_pairs, d_cells, d_cellof, d_spts, d_snrm,
+                                                      d_sidx);
         B2R_LAUNCH_CHECK(ctx);
     }
 
@@ -752,15 +787,18 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
     IcpArgs A;
     A.src_col = d_src_colors; A.s_it = d_sit; A.s_grad = d_sgrad;
     A.sqrt_lg = sqrt(params->lambda_geometric); A.sqrt_lp = sqrt(1.0 - params->lambda_geometric);
-    A.src = d_src_points; A.s_pts = d_spts; A.s_nrm = d_snrm; A.s_idx = d_sidx; A.keys = d_keys; A.starts = d_starts;
-    A.counts = d_counts; A.pairs = d_pairs; A.states = d_states; A.partials = d_partials; A.partial_stride = max_blocks;
+    A.src = d_src_points; A.s_pts = d_spts; A.s_nrm = d_snrm; A.s_idx = d_sidx; A.cells = d_cells; A.hit = d_hit;
+    A.hit_d2 = d_hitd2; A.pairs = d_pairs; A.states = d_states; A.partials = d_partials; A.partial_stride = max_blocks;
     A.corr = d_corr; A.r2 = params->max_correspondence_distance * params->max_correspondence_distance;
     A.rel_fitness = params->relative_fitness; A.rel_rmse = params->relative_rmse;
     A.max_iter = params->max_iteration < 0 ? 0 : params->max_iteration; A.estimation = params->estimation;
+    const dim3 sgrid(cdiv(std::max<long long>(max_ns, 1), ICP_THREADS), n_pairs), agrid(max_blocks, n_pairs);
     for (int it = 0; it <= A.max_iter; ++it) {
-        if (A.estimation == 2) icp_iterate_kernel<2><<<dim3(max_blocks, n_pairs), ICP_THREADS, 0, st>>>(A);
-        else if (A.estimation == 1) icp_iterate_kernel<1><<<dim3(max_blocks, n_pairs), ICP_THREADS, 0, st>>>(A);
-        else icp_iterate_kernel<0><<<dim3(max_blocks, n_pairs), ICP_THREADS, 0, st>>>(A);
+        icp_search_kernel<<<sgrid, ICP_THREADS, 0, st>>>(A);
+        B2R_LAUNCH_CHECK(ctx);
+        if (A.estimation == 2) icp_accumulate_kernel<2><<<agrid, ICP_THREADS, 0, st>>>(A);
+        else if (A.estimation == 1) icp_accumulate_kernel<1><<<agrid, ICP_THREADS, 0, st>>>(A);
+        else icp_accumulate_kernel<0><<<agrid, ICP_THREADS, 0, st>>>(A);
         B2R_LAUNCH_CHECK(ctx);
     }
     B2R_CUDA(cudaMemcpyAsync(hs.data(), d_states, sizeof(IcpState) * n_pairs, cudaMemcpyDeviceToHost, st));
