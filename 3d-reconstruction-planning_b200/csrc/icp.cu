@@ -376,26 +376,31 @@ __global__ void __launch_bounds__(256) icp_gather_color_kernel(const double* __r
 
 // distance along one axis from the query to the cells `o` cells away from its own (em / ep: distance to the lower /
 // upper face of its own cell)
-__device__ __forceinline__ double icp_axis_dist(int o, double em, double ep, double h) {
-    return o == 0 ? 0.0 : (o < 0 ? (double)(-o - 1) * h + em : (double)(o - 1) * h + ep);
+__device__ __forceinline__ float icp_axis_dist(int o, float em, float ep, float h) {
+    return o == 0 ? 0.0f : (o < 0 ? (float)(-o - 1) * h + em : (float)(o - 1) * h + ep);
 }
 
-// candidates [m0, m1) of one run against the query: exact float64 distances, strict <, ties -> lowest target index
-__device__ __forceinline__ void icp_scan_run(const IcpArgs& A, uint32_t m0, uint32_t m1, double q0, double q1, double q2,
-                                             double& best, int& bestpos, int& bestj) {
-    for (uint32_t m = m0; m < m1; ++m) {
-        const double tx = __ldg(&A.s_pts[(long long)m * 3]) - q0;
-        const double ty = __ldg(&A.s_pts[(long long)m * 3 + 1]) - q1;
-        const double tz = __ldg(&A.s_pts[(long long)m * 3 + 2]) - q2;
-        const double d2 = tx * tx + ty * ty + tz * tz;
-        if (d2 < best) { best = d2; bestpos = (int)m; bestj = __ldg(&A.s_idx[m]); }
-        else if (d2 == best && bestpos >= 0) {
-            const int j = __ldg(&A.s_idx[m]);
-            if (j < bestj) { bestpos = (int)m; bestj = j; }
-        }
+// One candidate against the query: exact float64 distance, strict <, ties -> lowest target index.
+__device__ __forceinline__ void icp_candidate(const IcpArgs& A, uint32_t m, double q0, double q1, double q2, double& best,
+                                              int& bestpos, int& bestj) {
+    const double tx = __ldg(&A.s_pts[(long long)m * 3]) - q0;
+    const double ty = __ldg(&A.s_pts[(long long)m * 3 + 1]) - q1;
+    const double tz = __ldg(&A.s_pts[(long long)m * 3 + 2]) - q2;
+    const double d2 = tx * tx + ty * ty + tz * tz;
+    if (d2 < best) { best = d2; bestpos = (int)m; bestj = __ldg(&A.s_idx[m]); }
+    else if (d2 == best && bestpos >= 0) {
+        const int j = __ldg(&A.s_idx[m]);
+        if (j < bestj) { bestpos = (int)m; bestj = j; }
     }
 }
 
+// The search, a thread per source point.  What the first version of this kernel cost was not arithmetic but divergence:
+// nested ring / row / trim / candidate loops with per-lane trip counts left 12.5 of 32 lanes active per instruction
+// (profiles/r02_icp_search_4mm_ncu.txt: 578 M warp instructions per launch of 16 pairs).  Now rings 0 and 1 -- where
+// almost every query ends -- are straight-line code: the own cell, then the three z planes of the 3x3x3 neighbourhood,
+// each plane's (up to four) candidate runs walked by ONE flattened loop; rows and end cells that cannot hold a closer
+// point are dropped from per-query face distances (float32 with a 1e-5 margin: conservative), the runs' ends are loaded
+// together.  Rings >= 2 (queries without a neighbour within a cell size) keep the generic loop.
 __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid_constant__ IcpArgs A) {
     const int p = blockIdx.y;
     const IcpState& St = A.states[p];
@@ -426,50 +431,103 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
         const double g0 = (q0 - P.gmin[0]) * P.inv_h, g1 = (q1 - P.gmin[1]) * P.inv_h, g2 = (q2 - P.gmin[2]) * P.inv_h;
         const double fl0 = floor(g0), fl1 = floor(g1), fl2 = floor(g2);
         const int c0 = (int)fl0, c1 = (int)fl1, c2 = (int)fl2;       // may lie outside the grid (within r of the box)
-        const double em0 = (g0 - fl0) * h, ep0 = h - em0, em1 = (g1 - fl1) * h, ep1 = h - em1, em2 = (g2 - fl2) * h, ep2 = h - em2;
-        const double face = fmin(fmin(fmin(em0, ep0), fmin(em1, ep1)), fmin(em2, ep2));
         const int nx = P.nx, ny = P.ny, nz = P.nz;
         const uint32_t* E = A.cells + P.cell_off;
-        for (int ring = 0; ring <= P.rings + 1; ++ring) {
-            if (ring > 0) {
-                const double lo = (double)(ring - 1) * h + face;   // everything in ring >= `ring` is at least this far
-                if (lo * lo >= best) break;
+        // distances to the faces of the own cell, float32 (pruning only; every prune leaves a 1e-5 relative margin)
+        const float hf = (float)h;
+        const float em0 = (float)(g0 - fl0) * hf, ep0 = hf - em0, em1 = (float)(g1 - fl1) * hf, ep1 = hf - em1;
+        const float em2 = (float)(g2 - fl2) * hf, ep2 = hf - em2;
+        const float face = fminf(fminf(fminf(em0, ep0), fminf(em1, ep1)), fminf(em2, ep2));
+        // ---- ring 0: the own cell ----
+        if ((unsigned)c0 < (unsigned)nx && (unsigned)c1 < (unsigned)ny && (unsigned)c2 < (unsigned)nz) {
+            const uint32_t* row = E + ((long long)c2 * ny + c1) * nx + c0;
+            const uint32_t m1 = __ldg(row);
+            for (uint32_t m = __ldg(row - 1); m < m1; ++m) icp_candidate(A, m, q0, q1, q2, best, bestpos, bestj);
+        }
+        // ---- ring 1: three planes, straight-line; skipped when nothing outside the own cell can be closer ----
+        if (!(face * face * 0.99999f >= (float)best)) {
+            const float dx2m = em0 * em0 * 0.99999f, dx2p = ep0 * ep0 * 0.99999f;
+#pragma unroll
+            for (int pz = 0; pz < 3; ++pz) {
+                const int dz = pz == 0 ? 0 : (pz == 1 ? -1 : 1);           // the query's own plane first
+                const int cz = c2 + dz;
+                const float dz2 = dz == 0 ? 0.0f : (dz < 0 ? em2 * em2 : ep2 * ep2) * 0.99999f;
+                const float thr = (float)best * 1.00001f + 1e-30f;
+                const bool okz = (unsigned)cz < (unsigned)nz && dz2 <= thr;
+                uint32_t ra[4], rn[4];          // up to four runs: start, length
+#pragma unroll
+                for (int py = 0; py < 3; ++py) {
+                    const int dy = py - 1;
+                    const int cy = c1 + dy;
+                    const float row2 = dz2 + (dy == 0 ? 0.0f : (dy < 0 ? em1 * em1 : ep1 * ep1) * 0.99999f);
+                    const bool ok = okz && (unsigned)cy < (unsigned)ny && row2 <= thr;
+                    const bool centre = (dz == 0 && dy == 0);
+                    const bool inl = ok && row2 + dx2m <= thr, inr = ok && row2 + dx2p <= thr;
+                    const uint32_t* row = E + ((long long)(ok ? cz : 0) * ny + (ok ? cy : 0)) * nx;
+                    if (!centre) {
+                        int xa = inl ? c0 - 1 : c0, xb = inr ? c0 + 1 : c0;
+                        xa = max(xa, 0); xb = min(xb, nx - 1);
+                        const bool run = ok && xa <= xb;
+                        const uint32_t a0 = run ? __ldg(row + xa - 1) : 0u, a1 = run ? __ldg(row + xb) : 0u;
+                        ra[py] = a0; rn[py] = a1 - a0;
+                        if (dz != 0 && py == 2) { ra[3] = 0u; rn[3] = 0u; }
+                    } else {                                                // own cell is done: its two x neighbours
+                        const bool rl = inl && c0 - 1 >= 0 && c0 - 1 < nx, rr = inr && c0 + 1 >= 0 && c0 + 1 < nx;
+                        const uint32_t l0 = rl ? __ldg(row + c0 - 2) : 0u, l1 = rl ? __ldg(row + c0 - 1) : 0u;
+                        const uint32_t r0 = rr ? __ldg(row + c0) : 0u, r1 = rr ? __ldg(row + c0 + 1) : 0u;
+                        ra[1] = l0; rn[1] = l1 - l0;
+                        ra[3] = r0; rn[3] = r1 - r0;
+                    }
+                }
+                // one flattened loop over the plane's runs
+                const uint32_t s1 = rn[0], s2 = s1 + rn[1], s3 = s2 + rn[2], tot = s3 + rn[3];
+                const uint32_t o0 = ra[0], o1 = ra[1] - s1, o2 = ra[2] - s2, o3 = ra[3] - s3;
+                for (uint32_t t = 0; t < tot; ++t) {
+                    const uint32_t m = t + (t < s1 ? o0 : (t < s2 ? o1 : (t < s3 ? o2 : o3)));
+                    icp_candidate(A, m, q0, q1, q2, best, bestpos, bestj);
+                }
+            }
+        }
+        // ---- rings >= 2 (rare): generic walk, a shell row is one run, an inner row contributes its two end cells ----
+        for (int ring = 2; ring <= P.rings + 1; ++ring) {
+            {
+                const float lo = (float)(ring - 1) * hf + face;   // everything in ring >= `ring` is at least this far
+                if (lo * lo * 0.99999f >= (float)best) break;
             }
             for (int dz = -ring; dz <= ring; ++dz) {
                 const int cz = c2 + dz;
                 if ((unsigned)cz >= (unsigned)nz) continue;
-                const double ez = icp_axis_dist(dz, em2, ep2, h);
+                const float ez = (float)icp_axis_dist(dz, em2, ep2, hf);
                 for (int dy = -ring; dy <= ring; ++dy) {
                     const int cy = c1 + dy;
                     if ((unsigned)cy >= (unsigned)ny) continue;
-                    const double ey = icp_axis_dist(dy, em1, ep1, h);
-                    const double row2 = ey * ey + ez * ez;
-                    // slack of a few ulps: the cell of a point was computed with rounded arithmetic
-                    if (row2 > best * (1.0 + 1e-9) + 1e-24) continue;
+                    const float ey = (float)icp_axis_dist(dy, em1, ep1, hf);
+                    const float row2 = (ey * ey + ez * ez) * 0.99999f;
+                    if (row2 > (float)best * 1.00001f + 1e-30f) continue;
                     const uint32_t* row = E + ((long long)cz * ny + cy) * nx;
                     const bool shell = (dz == -ring || dz == ring || dy == -ring || dy == ring);
-                    // a shell row (and ring 0) is ONE run of x cells; an inner row contributes its two end cells
-                    const int nseg = (shell || ring == 0) ? 1 : 2;
+                    const int nseg = shell ? 1 : 2;
                     for (int sg = 0; sg < nseg; ++sg) {
                         int xa, xb;
                         if (nseg == 1) { xa = -ring; xb = ring; }
                         else { xa = xb = (sg == 0 ? -ring : ring); }
                         // trim cells whose box is farther than the best distance so far from both ends of the run
-                        const double thr = best * (1.0 + 1e-9) + 1e-24 - row2;
+                        const float thr = (float)best * 1.00001f + 1e-30f - row2;
                         while (xa <= xb) {
-                            const double ex = icp_axis_dist(xa, em0, ep0, h);
-                            if (ex * ex <= thr) break;
+                            const float ex = (float)icp_axis_dist(xa, em0, ep0, hf);
+                            if (ex * ex * 0.99999f <= thr) break;
                             ++xa;
                         }
                         while (xb >= xa) {
-                            const double ex = icp_axis_dist(xb, em0, ep0, h);
-                            if (ex * ex <= thr) break;
+                            const float ex = (float)icp_axis_dist(xb, em0, ep0, hf);
+                            if (ex * ex * 0.99999f <= thr) break;
                             --xb;
                         }
                         xa = max(xa + c0, 0);
                         xb = min(xb + c0, nx - 1);
                         if (xa > xb) continue;
-                        icp_scan_run(A, __ldg(row + xa - 1), __ldg(row + xb), q0, q1, q2, best, bestpos, bestj);
+                        const uint32_t m1 = __ldg(row + xb);
+                        for (uint32_t m = __ldg(row + xa - 1); m < m1; ++m) icp_candidate(A, m, q0, q1, q2, best, bestpos, bestj);
                     }
                 }
             }
