@@ -162,7 +162,8 @@ __global__ void __launch_bounds__(256) icp_cell_scatter_kernel(const double* __r
     const long long g = P.tgt_off + i;
     const uint32_t pos = atomicAdd(&cells[P.cell_off + cell_of[g]], 1u);      // batch-wide sorted index
 #pragma unroll
-    for (int k = 0; k < 3; ++k) s_pts[(long long)pos * 3 + k] = tgt[g * 3 + k];
+    for (int k = 0; k < 3; ++k) s_pts[(long long)pos * 4 + k] = tgt[g * 3 + k];
+    s_pts[(long long)pos * 4 + 3] = __longlong_as_double((long long)i);      // the point's index in its cloud rides along
     if (nrm && s_nrm) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) s_nrm[(long long)pos * 3 + k] = nrm[g * 3 + k];
@@ -338,7 +339,7 @@ __device__ void matmul4(const double* A, const double* B, double* C) {
 
 struct IcpArgs {
     const double* src;
-    const double* s_pts;
+    const double* s_pts;       // cell-sorted target points, 32 bytes each: x, y, z, original index (integer bits)
     const double* s_nrm;
     const int32_t* s_idx;
     const uint32_t* cells;     // per cell: END of its run in the sorted arrays (cells[-1] = 0 exists)
@@ -380,19 +381,34 @@ __device__ __forceinline__ float icp_axis_dist(int o, float em, float ep, float 
     return o == 0 ? 0.0f : (o < 0 ? (float)(-o - 1) * h + em : (float)(o - 1) * h + ep);
 }
 
-// One candidate against the query: exact float64 distance, strict <, ties -> lowest target index.
-__device__ __forceinline__ void icp_candidate(const IcpArgs& A, uint32_t m, double q0, double q1, double q2, double& best,
-                                              int& bestpos, int& bestj) {
-    const double tx = __ldg(&A.s_pts[(long long)m * 3]) - q0;
-    const double ty = __ldg(&A.s_pts[(long long)m * 3 + 1]) - q1;
-    const double tz = __ldg(&A.s_pts[(long long)m * 3 + 2]) - q2;
-    const double d2 = tx * tx + ty * ty + tz * tz;
-    if (d2 < best) { best = d2; bestpos = (int)m; bestj = __ldg(&A.s_idx[m]); }
-    else if (d2 == best && bestpos >= 0) {
-        const int j = __ldg(&A.s_idx[m]);
-        if (j < bestj) { bestpos = (int)m; bestj = j; }
-    }
+// One candidate against the query: exact float64 distance, strict <, ties -> lowest target index.  A sorted point is
+// one aligned 32-byte record {x, y, z, index}: two 16-byte loads, no dependent index load.
+struct IcpCand { double x, y, z; int j; };
+__device__ __forceinline__ IcpCand icp_load(const IcpArgs& A, uint32_t m) {
+    const double2 a = __ldg(reinterpret_cast<const double2*>(A.s_pts + (long long)m * 4));
+    const double2 b = __ldg(reinterpret_cast<const double2*>(A.s_pts + (long long)m * 4 + 2));
+    return IcpCand{a.x, a.y, b.x, (int)__double_as_longlong(b.y)};
 }
+__device__ __forceinline__ void icp_candidate(const IcpCand& c, uint32_t m, double q0, double q1, double q2, double& best,
+                                              int& bestpos, int& bestj) {
+    const double tx = c.x - q0, ty = c.y - q1, tz = c.z - q2;
+    const double d2 = tx * tx + ty * ty + tz * tz;
+    if (d2 < best || (d2 == best && bestpos >= 0 && c.j < bestj)) { best = d2; bestpos = (int)m; bestj = c.j; }
+}
+// A run of candidates [m0, m0 + n) given as t -> m (IDX), four per turn with their loads in flight together (the serial
+// load -> compare -> branch -> next load chain was what the kernel waited on: 8 stall cycles per issue on the long
+// scoreboard).  The last turn repeats the final candidate, which changes nothing.
+#define B2R_ICP_SCAN(TOT, IDX)                                                                   \
+    for (uint32_t t = 0; t < (TOT); t += 4) {                                                    \
+        uint32_t mm[4];                                                                          \
+        IcpCand cc[4];                                                                           \
+        _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                          \
+            const uint32_t tt = min(t + (uint32_t)u, (TOT) - 1u);                                \
+            mm[u] = IDX(tt);                                                                     \
+            cc[u] = icp_load(A, mm[u]);                                                          \
+        }                                                                                        \
+        _Pragma("unroll") for (int u = 0; u < 4; ++u) icp_candidate(cc[u], mm[u], q0, q1, q2, best, bestpos, bestj); \
+    }
 
 // The search, a thread per source point.  What the first version of this kernel cost was not arithmetic but divergence:
 // nested ring / row / trim / candidate loops with per-lane trip counts left 12.5 of 32 lanes active per instruction
@@ -441,8 +457,10 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
         // ---- ring 0: the own cell ----
         if ((unsigned)c0 < (unsigned)nx && (unsigned)c1 < (unsigned)ny && (unsigned)c2 < (unsigned)nz) {
             const uint32_t* row = E + ((long long)c2 * ny + c1) * nx + c0;
-            const uint32_t m1 = __ldg(row);
-            for (uint32_t m = __ldg(row - 1); m < m1; ++m) icp_candidate(A, m, q0, q1, q2, best, bestpos, bestj);
+            const uint32_t m0 = __ldg(row - 1), n0 = __ldg(row) - m0;
+#define B2R_IDX0(T) (m0 + (T))
+            B2R_ICP_SCAN(n0, B2R_IDX0)
+#undef B2R_IDX0
         }
         // ---- ring 1: three planes, straight-line; skipped when nothing outside the own cell can be closer ----
         if (!(face * face * 0.99999f >= (float)best)) {
@@ -482,10 +500,9 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
                 // one flattened loop over the plane's runs
                 const uint32_t s1 = rn[0], s2 = s1 + rn[1], s3 = s2 + rn[2], tot = s3 + rn[3];
                 const uint32_t o0 = ra[0], o1 = ra[1] - s1, o2 = ra[2] - s2, o3 = ra[3] - s3;
-                for (uint32_t t = 0; t < tot; ++t) {
-                    const uint32_t m = t + (t < s1 ? o0 : (t < s2 ? o1 : (t < s3 ? o2 : o3)));
-                    icp_candidate(A, m, q0, q1, q2, best, bestpos, bestj);
-                }
+#define B2R_IDX4(T) ((T) + ((T) < s1 ? o0 : ((T) < s2 ? o1 : ((T) < s3 ? o2 : o3))))
+                B2R_ICP_SCAN(tot, B2R_IDX4)
+#undef B2R_IDX4
             }
         }
         // ---- rings >= 2 (rare): generic walk, a shell row is one run, an inner row contributes its two end cells ----
@@ -526,8 +543,10 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
                         xa = max(xa + c0, 0);
                         xb = min(xb + c0, nx - 1);
                         if (xa > xb) continue;
-                        const uint32_t m1 = __ldg(row + xb);
-                        for (uint32_t m = __ldg(row + xa - 1); m < m1; ++m) icp_candidate(A, m, q0, q1, q2, best, bestpos, bestj);
+                        const uint32_t mg = __ldg(row + xa - 1), ng = __ldg(row + xb) - mg;
+#define B2R_IDXG(T) (mg + (T))
+                        B2R_ICP_SCAN(ng, B2R_IDXG)
+#undef B2R_IDXG
                     }
                 }
             }
@@ -566,7 +585,7 @@ __global__ void __launch_bounds__(ICP_THREADS, 2) icp_accumulate_kernel(const __
         const double sx = s[0], sy = s[1], sz = s[2];
         const double q[3] = {T[0] * sx + T[1] * sy + T[2] * sz + T[3], T[4] * sx + T[5] * sy + T[6] * sz + T[7],
                              T[8] * sx + T[9] * sy + T[10] * sz + T[11]};
-        const double tx = A.s_pts[bestpos * 3], ty = A.s_pts[bestpos * 3 + 1], tz = A.s_pts[bestpos * 3 + 2];
+        const double tx = A.s_pts[bestpos * 4], ty = A.s_pts[bestpos * 4 + 1], tz = A.s_pts[bestpos * 4 + 2];
         acc[0] += 1.0;
         acc[1] += best;
         if (EST == 2) {
@@ -771,12 +790,12 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
     IcpPair* d_pairs = (IcpPair*)ctx->icp_a.ptr;
     IcpState* d_states = (IcpState*)((char*)ctx->icp_a.ptr + sz_pairs);
     long long* d_bb = (long long*)((char*)ctx->icp_a.ptr + sz_pairs + sz_states);
-    const size_t sz_pts = al(sizeof(double) * 3 * (size_t)Nt);
-    if (ctx->icp_c.ensure(2 * sz_pts + al(sizeof(int32_t) * (size_t)Nt) + al(sizeof(uint32_t) * (size_t)Nt))) return -102;
+    const size_t sz_pts = al(sizeof(double) * 3 * (size_t)Nt), sz_pts4 = al(sizeof(double) * 4 * (size_t)Nt);
+    if (ctx->icp_c.ensure(sz_pts4 + sz_pts + al(sizeof(int32_t) * (size_t)Nt) + al(sizeof(uint32_t) * (size_t)Nt))) return -102;
     double* d_spts = (double*)ctx->icp_c.ptr;
-    double* d_snrm = (double*)((char*)ctx->icp_c.ptr + sz_pts);
-    int32_t* d_sidx = (int32_t*)((char*)ctx->icp_c.ptr + 2 * sz_pts);
-    uint32_t* d_cellof = (uint32_t*)((char*)ctx->icp_c.ptr + 2 * sz_pts + al(sizeof(int32_t) * (size_t)Nt));
+    double* d_snrm = (double*)((char*)ctx->icp_c.ptr + sz_pts4);
+    int32_t* d_sidx = (int32_t*)((char*)ctx->icp_c.ptr + sz_pts4 + sz_pts);
+    uint32_t* d_cellof = (uint32_t*)((char*)ctx->icp_c.ptr + sz_pts4 + sz_pts + al(sizeof(int32_t) * (size_t)Nt));
     if (ctx->icp_d.ensure(sizeof(double) * ICP_NACC * (size_t)max_blocks * n_pairs)) return -102;
     double* d_partials = (double*)ctx->icp_d.ptr;
     if (ctx->icp_f.ensure(al(sizeof(int32_t) * (size_t)Ns) + al(sizeof(double) * (size_t)Ns) + 256)) return -102;
