@@ -44,6 +44,7 @@ struct IcpPair {
     double gmin[3];            // grid origin
     double h, inv_h;
     double bmin[3], bmax[3];   // target bounding box
+    float feps;                // bound on |float32 (t - q) - exact (t - q)| for grid-relative float32 coordinates
 };
 
 struct IcpState {
@@ -127,6 +128,11 @@ static void icp_grid_setup(IcpPair& P, const double* bmin, const double* bmax, d
     if (P.rings < 1) P.rings = 1;
     for (int k = 0; k < 3; ++k) P.gmin[k] = P.bmin[k] - h;
     P.nx = (int)floor(e[0] / h) + 3; P.ny = (int)floor(e[1] / h) + 3; P.nz = (int)floor(e[2] / h) + 3;
+    // float32 pre-filter of the candidates: target and query coordinates relative to gmin are at most ext in magnitude,
+    // each rounds to float32 with error <= ext * 2^-24, so a difference vector is off by <= sqrt(3) * 2 * ext * 2^-24
+    // (~2.1e-7 ext); x2 for the float32 arithmetic on top
+    const double ext = fmax(e[0], fmax(e[1], e[2])) + 2.0 * h + 2.0 * r;
+    P.feps = (float)(4.2e-7 * ext);
 }
 
 // cell of a target point (inside the grid by construction; clamped against rounding at the box faces)
@@ -155,7 +161,7 @@ __global__ void __launch_bounds__(256) icp_cell_scatter_kernel(const double* __r
                                                                const IcpPair* __restrict__ pairs, uint32_t* __restrict__ cells,
                                                                const uint32_t* __restrict__ cell_of,
                                                                double* __restrict__ s_pts, double* __restrict__ s_nrm,
-                                                               int32_t* __restrict__ s_idx) {
+                                                               int32_t* __restrict__ s_idx, float4* __restrict__ s_ptsf) {
     const IcpPair P = pairs[blockIdx.y];
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.n_tgt) return;
@@ -169,6 +175,8 @@ __global__ void __launch_bounds__(256) icp_cell_scatter_kernel(const double* __r
         for (int k = 0; k < 3; ++k) s_nrm[(long long)pos * 3 + k] = nrm[g * 3 + k];
     }
     s_idx[pos] = (int32_t)i;
+    s_ptsf[pos] = make_float4((float)(tgt[g * 3] - P.gmin[0]), (float)(tgt[g * 3 + 1] - P.gmin[1]), (float)(tgt[g * 3 + 2] - P.gmin[2]),
+                              __int_as_float((int)i));
 }
 
 // ---- small dense solvers (one thread) ---------------------------------------------------------------
@@ -340,6 +348,7 @@ __device__ void matmul4(const double* A, const double* B, double* C) {
 struct IcpArgs {
     const double* src;
     const double* s_pts;       // cell-sorted target points, 32 bytes each: x, y, z, original index (integer bits)
+    const float4* s_ptsf;      // the same as float32 relative to the grid origin (pre-filter), .w = index bits
     const double* s_nrm;
     const int32_t* s_idx;
     const uint32_t* cells;     // per cell: END of its run in the sorted arrays (cells[-1] = 0 exists)
@@ -381,33 +390,49 @@ __device__ __forceinline__ float icp_axis_dist(int o, float em, float ep, float 
     return o == 0 ? 0.0f : (o < 0 ? (float)(-o - 1) * h + em : (float)(o - 1) * h + ep);
 }
 
-// One candidate against the query: exact float64 distance, strict <, ties -> lowest target index.  A sorted point is
-// one aligned 32-byte record {x, y, z, index}: two 16-byte loads, no dependent index load.
-struct IcpCand { double x, y, z; int j; };
-__device__ __forceinline__ IcpCand icp_load(const IcpArgs& A, uint32_t m) {
+// Candidates are pre-filtered in float32 (one 16-byte load, six float operations): grid-relative float32 coordinates
+// give the squared distance to within the bound `feps` on the difference vector, so a candidate whose float32 distance
+// exceeds sqrt(best) + feps (with a relative margin for the float32 arithmetic) cannot be the nearest neighbour nor tie
+// with it.  Everything that passes is decided in float64 exactly as before: strict <, ties -> lowest target index.
+struct IcpBest {
+    double best;      // exact squared distance of the best candidate so far (r^2 before the first)
+    float thr;        // float32 pass threshold derived from it
+    int pos, j;
+};
+__device__ __forceinline__ float icp_thr(double best, float feps) {
+    float sq;       // (MUFU approximation, 2 ulp: far inside the 1e-5 margins; the IEEE sqrtf sequence was 17 % of the kernel)
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(sq) : "f"((float)best));
+    const float s = sq * 1.00001f + feps;
+    return s * s * 1.00001f;
+}
+__device__ __forceinline__ void icp_exact(const IcpArgs& A, uint32_t m, double q0, double q1, double q2, float feps, IcpBest& B) {
     const double2 a = __ldg(reinterpret_cast<const double2*>(A.s_pts + (long long)m * 4));
     const double2 b = __ldg(reinterpret_cast<const double2*>(A.s_pts + (long long)m * 4 + 2));
-    return IcpCand{a.x, a.y, b.x, (int)__double_as_longlong(b.y)};
-}
-__device__ __forceinline__ void icp_candidate(const IcpCand& c, uint32_t m, double q0, double q1, double q2, double& best,
-                                              int& bestpos, int& bestj) {
-    const double tx = c.x - q0, ty = c.y - q1, tz = c.z - q2;
+    const int j = (int)__double_as_longlong(b.y);
+    const double tx = a.x - q0, ty = a.y - q1, tz = b.x - q2;
     const double d2 = tx * tx + ty * ty + tz * tz;
-    if (d2 < best || (d2 == best && bestpos >= 0 && c.j < bestj)) { best = d2; bestpos = (int)m; bestj = c.j; }
+    if (d2 < B.best || (d2 == B.best && B.pos >= 0 && j < B.j)) {
+        B.best = d2; B.pos = (int)m; B.j = j;
+        B.thr = icp_thr(d2, feps);
+    }
 }
-// A run of candidates [m0, m0 + n) given as t -> m (IDX), four per turn with their loads in flight together (the serial
-// load -> compare -> branch -> next load chain was what the kernel waited on: 8 stall cycles per issue on the long
-// scoreboard).  The last turn repeats the final candidate, which changes nothing.
+// A run of candidates given as t -> m (IDX), four per turn with their loads in flight together (the serial load ->
+// compare -> branch -> next load chain was what the kernel waited on).  The last turn repeats the final candidate,
+// which changes nothing.
 #define B2R_ICP_SCAN(TOT, IDX)                                                                   \
     for (uint32_t t = 0; t < (TOT); t += 4) {                                                    \
         uint32_t mm[4];                                                                          \
-        IcpCand cc[4];                                                                           \
+        float4 cc[4];                                                                            \
         _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                          \
             const uint32_t tt = min(t + (uint32_t)u, (TOT) - 1u);                                \
             mm[u] = IDX(tt);                                                                     \
-            cc[u] = icp_load(A, mm[u]);                                                          \
+            cc[u] = __ldg(A.s_ptsf + mm[u]);                                                     \
         }                                                                                        \
-        _Pragma("unroll") for (int u = 0; u < 4; ++u) icp_candidate(cc[u], mm[u], q0, q1, q2, best, bestpos, bestj); \
+        _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                          \
+            const float fx = cc[u].x - qf0, fy = cc[u].y - qf1, fz = cc[u].z - qf2;              \
+            const float d2f = __fmaf_rn(fz, fz, __fmaf_rn(fy, fy, fx * fx));                     \
+            if (d2f <= B.thr) icp_exact(A, mm[u], q0, q1, q2, feps, B);                          \
+        }                                                                                        \
     }
 
 // The search, a thread per source point.  What the first version of this kernel cost was not arithmetic but divergence:
@@ -429,9 +454,9 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
     const double q0 = St.T[0] * sx + St.T[1] * sy + St.T[2] * sz + St.T[3];
     const double q1 = St.T[4] * sx + St.T[5] * sy + St.T[6] * sz + St.T[7];
     const double q2 = St.T[8] * sx + St.T[9] * sy + St.T[10] * sz + St.T[11];
-    double best = A.r2;
-    int bestpos = -1;
-    int bestj = 0x7fffffff;
+    const float feps = P.feps;
+    IcpBest B{A.r2, icp_thr(A.r2, feps), -1, 0x7fffffff};
+    const float qf0 = (float)(q0 - P.gmin[0]), qf1 = (float)(q1 - P.gmin[1]), qf2 = (float)(q2 - P.gmin[2]);
     // reject queries farther than r from the target's bounding box
     double bd = 0.0;
     {
@@ -463,14 +488,14 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
 #undef B2R_IDX0
         }
         // ---- ring 1: three planes, straight-line; skipped when nothing outside the own cell can be closer ----
-        if (!(face * face * 0.99999f >= (float)best)) {
+        if (!(face * face * 0.99999f >= (float)B.best)) {
             const float dx2m = em0 * em0 * 0.99999f, dx2p = ep0 * ep0 * 0.99999f;
 #pragma unroll
             for (int pz = 0; pz < 3; ++pz) {
                 const int dz = pz == 0 ? 0 : (pz == 1 ? -1 : 1);           // the query's own plane first
                 const int cz = c2 + dz;
                 const float dz2 = dz == 0 ? 0.0f : (dz < 0 ? em2 * em2 : ep2 * ep2) * 0.99999f;
-                const float thr = (float)best * 1.00001f + 1e-30f;
+                const float thr = (float)B.best * 1.00001f + 1e-30f;
                 const bool okz = (unsigned)cz < (unsigned)nz && dz2 <= thr;
                 uint32_t ra[4], rn[4];          // up to four runs: start, length
 #pragma unroll
@@ -509,7 +534,7 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
         for (int ring = 2; ring <= P.rings + 1; ++ring) {
             {
                 const float lo = (float)(ring - 1) * hf + face;   // everything in ring >= `ring` is at least this far
-                if (lo * lo * 0.99999f >= (float)best) break;
+                if (lo * lo * 0.99999f >= (float)B.best) break;
             }
             for (int dz = -ring; dz <= ring; ++dz) {
                 const int cz = c2 + dz;
@@ -520,7 +545,7 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
                     if ((unsigned)cy >= (unsigned)ny) continue;
                     const float ey = (float)icp_axis_dist(dy, em1, ep1, hf);
                     const float row2 = (ey * ey + ez * ez) * 0.99999f;
-                    if (row2 > (float)best * 1.00001f + 1e-30f) continue;
+                    if (row2 > (float)B.best * 1.00001f + 1e-30f) continue;
                     const uint32_t* row = E + ((long long)cz * ny + cy) * nx;
                     const bool shell = (dz == -ring || dz == ring || dy == -ring || dy == ring);
                     const int nseg = shell ? 1 : 2;
@@ -529,7 +554,7 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
                         if (nseg == 1) { xa = -ring; xb = ring; }
                         else { xa = xb = (sg == 0 ? -ring : ring); }
                         // trim cells whose box is farther than the best distance so far from both ends of the run
-                        const float thr = (float)best * 1.00001f + 1e-30f - row2;
+                        const float thr = (float)B.best * 1.00001f + 1e-30f - row2;
                         while (xa <= xb) {
                             const float ex = (float)icp_axis_dist(xa, em0, ep0, hf);
                             if (ex * ex * 0.99999f <= thr) break;
@@ -552,9 +577,9 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
             }
         }
     }
-    if (A.corr) A.corr[P.src_off + i] = bestpos >= 0 ? bestj : -1;
-    A.hit[P.src_off + i] = bestpos;
-    A.hit_d2[P.src_off + i] = best;
+    if (A.corr) A.corr[P.src_off + i] = B.pos >= 0 ? B.j : -1;
+    A.hit[P.src_off + i] = B.pos;
+    A.hit_d2[P.src_off + i] = B.best;
 }
 
 template <int EST>
@@ -791,11 +816,13 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
     IcpState* d_states = (IcpState*)((char*)ctx->icp_a.ptr + sz_pairs);
     long long* d_bb = (long long*)((char*)ctx->icp_a.ptr + sz_pairs + sz_states);
     const size_t sz_pts = al(sizeof(double) * 3 * (size_t)Nt), sz_pts4 = al(sizeof(double) * 4 * (size_t)Nt);
-    if (ctx->icp_c.ensure(sz_pts4 + sz_pts + al(sizeof(int32_t) * (size_t)Nt) + al(sizeof(uint32_t) * (size_t)Nt))) return -102;
+    const size_t sz_ptsf = al(sizeof(float4) * (size_t)Nt);
+    if (ctx->icp_c.ensure(sz_pts4 + sz_pts + al(sizeof(int32_t) * (size_t)Nt) + al(sizeof(uint32_t) * (size_t)Nt) + sz_ptsf)) return -102;
     double* d_spts = (double*)ctx->icp_c.ptr;
     double* d_snrm = (double*)((char*)ctx->icp_c.ptr + sz_pts4);
     int32_t* d_sidx = (int32_t*)((char*)ctx->icp_c.ptr + sz_pts4 + sz_pts);
     uint32_t* d_cellof = (uint32_t*)((char*)ctx->icp_c.ptr + sz_pts4 + sz_pts + al(sizeof(int32_t) * (size_t)Nt));
+    float4* d_sptsf = (float4*)((char*)ctx->icp_c.ptr + sz_pts4 + sz_pts + al(sizeof(int32_t) * (size_t)Nt) + al(sizeof(uint32_t) * (size_t)Nt));
     if (ctx->icp_d.ensure(sizeof(double) * ICP_NACC * (size_t)max_blocks * n_pairs)) return -102;
     double* d_partials = (double*)ctx->icp_d.ptr;
     if (ctx->icp_f.ensure(al(sizeof(int32_t) * (size_t)Ns) + al(sizeof(double) * (size_t)Ns) + 256)) return -102;
@@ -844,7 +871,7 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
         B2R_LAUNCH_CHECK(ctx);
         if (int rc = scan_exclusive_u32(ctx, d_cells, d_cells, cell_total, nullptr, st)) return rc;
         icp_cell_scatter_kernel<<<grid, 256, 0, st>>>(d_tgt_points, d_tgt_normals, d_pairs, d_cells, d_cellof, d_spts, d_snrm,
-                                                      d_sidx);
+                                                      d_sidx, d_sptsf);
         B2R_LAUNCH_CHECK(ctx);
     }
 
@@ -864,7 +891,7 @@ extern "C" int b2r_icp_batch(b2r_ctx* ctx, int n_pairs, const double* d_src_poin
     IcpArgs A;
     A.src_col = d_src_colors; A.s_it = d_sit; A.s_grad = d_sgrad;
     A.sqrt_lg = sqrt(params->lambda_geometric); A.sqrt_lp = sqrt(1.0 - params->lambda_geometric);
-    A.src = d_src_points; A.s_pts = d_spts; A.s_nrm = d_snrm; A.s_idx = d_sidx; A.cells = d_cells; A.hit = d_hit;
+    A.src = d_src_points; A.s_pts = d_spts; A.s_nrm = d_snrm; A.s_idx = d_sidx; A.s_ptsf = d_sptsf; A.cells = d_cells; A.hit = d_hit;
     A.hit_d2 = d_hitd2; A.pairs = d_pairs; A.states = d_states; A.partials = d_partials; A.partial_stride = max_blocks;
     A.corr = d_corr; A.r2 = params->max_correspondence_distance * params->max_correspondence_distance;
     A.rel_fitness = params->relative_fitness; A.rel_rmse = params->relative_rmse;
