@@ -248,6 +248,20 @@ class ScalableTSDFVolume:
     def reset(self):
         lib().orc_scalable_reset(self._h)
 
+    def set_bounds(self, unit_offset, n_units):
+        """Restrict the hash to the cube of `n_units`^3 units starting at `unit_offset` (unit indices) -- the product's
+        bounded backing cube; touches outside are counted (`clipped()`), not opened.  None removes the bound."""
+        if unit_offset is None:
+            lib().orc_scalable_set_bounds(self._h, None, None)
+            return
+        lo = (C.c_int32 * 3)(*[int(v) for v in unit_offset])
+        hi = (C.c_int32 * 3)(*[int(v) + int(n_units) for v in unit_offset])
+        lib().orc_scalable_set_bounds(self._h, lo, hi)
+
+    def clipped(self):
+        lib().orc_scalable_clipped.restype = C.c_int64
+        return int(lib().orc_scalable_clipped(self._h))
+
     def integrate(self, depth_f32, color, K, extrinsic):
         depth_f32 = np.ascontiguousarray(depth_f32, np.float32)
         H, W = depth_f32.shape

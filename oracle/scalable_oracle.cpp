@@ -48,6 +48,12 @@ struct OrcScalable {
     std::vector<UKey> order;   // opening order (only to make the export deterministic)
     std::vector<double> verts, vcols, normals;
     std::vector<int32_t> tris;
+    // optional bounding cube in unit indices [blo, bhi): units outside are not opened (counted in `clipped`).  Open3D
+    // has no such bound; it is what the product's bounded dense backing cube does (b2r_integrate_units counts the same
+    // touches), so that a CPU / GPU throughput pair compares the same work.
+    bool bounded = false;
+    int blo[3] = {0, 0, 0}, bhi[3] = {0, 0, 0};
+    int64_t clipped = 0;
 
     const OrcVolume* find(const UKey& k) const {
         auto it = units.find(k);
@@ -124,7 +130,13 @@ void* orc_scalable_create(double voxel_length, double sdf_trunc, int color_type,
     return s;
 }
 void orc_scalable_destroy(void* h) { delete (OrcScalable*)h; }
-void orc_scalable_reset(void* h) { OrcScalable* s = (OrcScalable*)h; s->units.clear(); s->order.clear(); }
+void orc_scalable_reset(void* h) { OrcScalable* s = (OrcScalable*)h; s->units.clear(); s->order.clear(); s->clipped = 0; }
+void orc_scalable_set_bounds(void* h, const int32_t* lo, const int32_t* hi) {
+    OrcScalable* s = (OrcScalable*)h;
+    s->bounded = lo && hi;
+    for (int a = 0; a < 3 && s->bounded; ++a) { s->blo[a] = lo[a]; s->bhi[a] = hi[a]; }
+}
+int64_t orc_scalable_clipped(void* h) { return ((OrcScalable*)h)->clipped; }
 int64_t orc_scalable_num_units(void* h) { return (int64_t)((OrcScalable*)h)->order.size(); }
 void orc_scalable_unit_keys(void* h, int32_t* out) {
     OrcScalable* s = (OrcScalable*)h;
@@ -168,6 +180,11 @@ int64_t orc_scalable_integrate(void* h, const float* depth, const void* color, i
                 for (int uy = lo[1]; uy <= hi[1]; ++uy)
                     for (int uz = lo[2]; uz <= hi[2]; ++uz) {
                         const UKey k{ux, uy, uz};
+                        if (s->bounded && (ux < s->blo[0] || ux >= s->bhi[0] || uy < s->blo[1] || uy >= s->bhi[1] ||
+                                           uz < s->blo[2] || uz >= s->bhi[2])) {
+                            ++s->clipped;
+                            continue;
+                        }
                         if (seen.insert(k).second) work.push_back(s->open(k));
                     }
         }

@@ -88,3 +88,27 @@ def test_scalable_agrees_with_uniform_near_the_surface(orc):
     assert np.quantile(d, 0.99) < 0.05 * VL
     P, N, _ = sv.extract_point_cloud()
     assert len(P) > 1000 and np.abs(np.linalg.norm(N, axis=1) - 1).max() < 1e-12
+
+
+def test_bounded_hash_is_the_unbounded_one_inside_the_cube(orc):
+    """`set_bounds` (what bench.py uses to give the CPU arm the product's bounded backing cube): the units inside the
+    cube are bit-identical to the unbounded hash's, units outside are not opened, and every touch outside is counted."""
+    frames, K = _frames(2)
+    a = orc.ScalableTSDFVolume(VL, TRUNC, 1, 16, 4)
+    b = orc.ScalableTSDFVolume(VL, TRUNC, 1, 16, 4)
+    for d16, rgb, ext in frames:
+        a.integrate(orc.depth_to_float(d16), rgb, hp.kt(K), ext)
+    ka = a.unit_keys()
+    lo = ka.min(axis=0) + 1                      # a cube that cuts one layer of units off on the low side of each axis
+    n = int((ka.max(axis=0) - lo).max()) + 1
+    b.set_bounds(lo, n)
+    for d16, rgb, ext in frames:
+        b.integrate(orc.depth_to_float(d16), rgb, hp.kt(K), ext)
+    kb = b.unit_keys()
+    inside = np.all((ka >= lo) & (ka < lo + n), axis=1)
+    assert 0 < inside.sum() < len(ka)
+    assert {tuple(k) for k in kb} == {tuple(k) for k in ka[inside]}
+    assert b.clipped() > 0 and a.clipped() == 0
+    for k in kb[::7]:
+        for x, y in zip(a.unit_arrays(k), b.unit_arrays(k)):
+            assert np.array_equal(x, y)

@@ -116,6 +116,9 @@ def sharded_mesh_bench(vol, ranges, voxel_length):
                              local=vol)
     sv.extract_triangle_mesh()                       # warm-up: scratch allocation, NCCL channel set-up
     sv._halo_valid = False
+    if world > 1:       # rank 0 has just copied the gathered mesh to the host: without this the other ranks' first
+        dist.barrier()  # phase (the halo exchange) would be charged rank 0's ~40 ms of host work
+    torch.cuda.synchronize(vol._ctx.tdev)
     sv.timings = {"on": True}
     t0 = time.perf_counter()
     mesh = sv.extract_triangle_mesh()
