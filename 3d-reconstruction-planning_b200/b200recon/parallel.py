@@ -347,7 +347,7 @@ class SlabVolume:
         """One-plane-below / two-planes-above halo of {tsdf, weight} and colour from the neighbour slabs."""
         if not self._halo_valid:
             self.local._ctx.join()   # the planes are sent straight from the volume's tensors
-            exchange_halos([self.local._tsdfw, self.local._color], self.z_end - self.z_begin, self.rank, self.world,
+            exchange_halos([self.local._tsdfw, self.local._color, self.local._rows], self.z_end - self.z_begin, self.rank, self.world,
                            self.group)
             self._halo_valid = True
 
@@ -502,7 +502,7 @@ class LocalSlabs:
         for k in range(len(self.slabs) - 1):
             a, b = self.slabs[k], self.slabs[k + 1]
             na = a.z_end - a.z_begin
-            for ta, tb in ((a._tsdfw, b._tsdfw), (a._color, b._color)):
+            for ta, tb in ((a._tsdfw, b._tsdfw), (a._color, b._color), (a._rows, b._rows)):
                 if ta is None:
                     continue
                 ta[lo + na:lo + na + hi].copy_(tb[lo:lo + hi])

@@ -51,9 +51,11 @@ class UniformTSDFVolume(TSDFVolume):
         self._color = None
         if self.color_type != TSDFVolumeColorType.NoColor:
             self._color = t.zeros((planes, R, R), dtype=t.int32, device=self._ctx.tdev)
+        # rows (plane, x) that may hold a voxel with weight != 0: extraction only reads cube rows next to one
+        self._rows = t.zeros((planes, R), dtype=t.uint8, device=self._ctx.tdev)
         self._desc = _lib.Volume(R, zb, ze, int(self.color_type), self.voxel_length, self.sdf_trunc,
                                  (C.c_double * 3)(*self.origin), self._tsdfw.data_ptr(),
-                                 0 if self._color is None else self._color.data_ptr())
+                                 0 if self._color is None else self._color.data_ptr(), self._rows.data_ptr())
         self._updates = t.zeros(1, dtype=t.int64, device=self._ctx.tdev)
         self.count_updates = False
 

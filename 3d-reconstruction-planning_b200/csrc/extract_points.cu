@@ -99,6 +99,41 @@ __global__ void __launch_bounds__(PC_THREADS) pc_count2_kernel(const float2* __r
     }
 }
 
+// Output-sensitive form (b2r_volume::d_rows, even R): a surface point needs a voxel with weight != 0, so a count block
+// (256 consecutive voxels) whose (plane, x) rows are all unmarked has nothing to count.  Persistent warps, a warp per count
+// block: one look at the marks, and only for marked rows the four 16-byte loads per lane; the counts are zeroed beforehand.
+// (Skipping inside pc_count2_kernel -- a block per 512 voxels with a barrier around the look -- was SLOWER than streaming
+// the whole cube: 2.66 ms vs 1.88 ms at 1024^3, two million block launches that do nothing.)
+__global__ void __launch_bounds__(256) pc_count_rows_kernel(const float2* __restrict__ tsdfw, const __grid_constant__ PcGeom G,
+                                                            uint32_t* __restrict__ blk_counts, int n_count_blocks,
+                                                            const uint8_t* __restrict__ rows) {
+    const int R = G.R, lane = threadIdx.x & 31;
+    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int nwarps = gridDim.x * 8;
+    for (int b = blockIdx.x * 8 + (threadIdx.x >> 5); b < n_count_blocks; b += nwarps) {
+        const int64_t t0 = (int64_t)b * PC_THREADS, t1 = min(t0 + PC_THREADS, n) - 1;
+        bool m = false;
+        for (int64_t r = t0 / R + lane; r <= t1 / R; r += 32) m |= __ldg(&rows[(int64_t)B2R_PAD_LO * R + r]) != 0;
+        if (!__any_sync(0xffffffffu, m)) continue;
+        unsigned c = 0;
+#pragma unroll
+        for (int k = 0; k < PC_THREADS / 64; ++k) {
+            const int64_t t = t0 + (int64_t)(k * 32 + lane) * 2;
+            if (t < n) {
+                const float4 q = __ldcs(reinterpret_cast<const float4*>(tsdfw + (int64_t)B2R_PAD_LO * R * R + t));
+                const bool va = pc_valid(make_float2(q.x, q.y)), vb = pc_valid(make_float2(q.z, q.w));
+                if (va | vb) {
+                    const int y = (int)(t % R), x = (int)((t / R) % R), z = G.z_begin + (int)(t / ((int64_t)R * R));
+                    if (va) c += __popc(pc_flags(tsdfw, G, x, y, z));
+                    if (vb) c += __popc(pc_flags(tsdfw, G, x, y + 1, z));
+                }
+            }
+        }
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (lane == 0) blk_counts[b] = c;
+    }
+}
+
 // raw per-block counts -> marks -> (scan) -> list of the blocks that produce points: the emit pass is a persistent
 // kernel over that list
 __global__ void __launch_bounds__(256) pc_mark_kernel(const uint32_t* __restrict__ blk_counts, int n, uint32_t* __restrict__ live) {
@@ -271,7 +306,10 @@ int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_poi
     uint32_t* live_list = blk + 3 * (size_t)nblocks;
     PcGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
              vol->color_type};
-    if (R % 2 == 0 && (((uintptr_t)vol->d_tsdfw) & 15) == 0)
+    if (vol->d_rows && R % 2 == 0 && (((uintptr_t)vol->d_tsdfw) & 15) == 0) {
+        B2R_CUDA(cudaMemsetAsync(blk, 0, (size_t)nblocks * sizeof(uint32_t), st));
+        pc_count_rows_kernel<<<ctx->sm_count * 8, 256, 0, st>>>((const float2*)vol->d_tsdfw, G, blk, nblocks, (const uint8_t*)vol->d_rows);
+    } else if (R % 2 == 0 && (((uintptr_t)vol->d_tsdfw) & 15) == 0)
         pc_count2_kernel<<<cdiv(nblocks, 2), PC_THREADS, 0, st>>>((const float2*)vol->d_tsdfw, G, blk, nblocks);
     else
         pc_count_kernel<<<nblocks, PC_THREADS, 0, st>>>((const float2*)vol->d_tsdfw, G, blk);

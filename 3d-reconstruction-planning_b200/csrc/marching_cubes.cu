@@ -51,11 +51,21 @@ __device__ __forceinline__ unsigned plane_nibble(const float2* __restrict__ tsdf
 // grid: (ceil(R/64), ceil(R/4), nchunks); block (64, 4): threadIdx.x -> y, threadIdx.y -> x
 __global__ void __launch_bounds__(256) mc_classify_kernel(const float2* __restrict__ tsdfw, uint8_t* __restrict__ code,
                                                           uint8_t* __restrict__ row_active, int R, int z_begin, int zc_lo,
-                                                          int zc_hi) {
+                                                          int zc_hi, const uint8_t* __restrict__ rows) {
     const int y = blockIdx.x * 64 + threadIdx.x;
     const int x = blockIdx.y * 4 + threadIdx.y;
     const int z0 = zc_lo + blockIdx.z * MC_ZCHUNK;
     const int z1 = min(z0 + MC_ZCHUNK, zc_hi + 1);  // cubes z0 .. z1-1
+    if (rows) {
+        // Output sensitivity (b2r_volume::d_rows): a cube of row (z, x) can only be active when rows (z, x), (z+1, x),
+        // (z, x+1), (z+1, x+1) all hold weights, and its code is only ever READ next to an active cube (see mc_live), so
+        // a block none of whose (z0..z1, x..x+4) rows is marked has nothing to classify and nothing anyone will read:
+        // it leaves without touching the volume (one ~165-byte look at the marks instead of 64 KB x 33 planes).
+        const int t = threadIdx.y * 64 + threadIdx.x;
+        const int zz = z0 + t / 5, xx = blockIdx.y * 4 + t % 5;
+        const bool m = t < 5 * (z1 - z0 + 1) && xx < R && rows[(int64_t)(zz - z_begin + B2R_PAD_LO) * R + xx] != 0;
+        if (!__syncthreads_or(m)) return;
+    }
     if (x >= R || y >= R || z0 >= z1) return;
     const bool edge = (x >= R - 1) || (y >= R - 1);
     if (edge) {  // no cube starts on the last row/column
@@ -323,13 +333,15 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
     if (ctx->mc_flags.ensure(planes * R)) return -102;
     uint8_t* row_active = (uint8_t*)ctx->mc_flags.ptr;
     B2R_CUDA(cudaMemsetAsync(row_active, 0, planes * R, st));
-    B2R_CUDA(cudaMemsetAsync(code, 0, nvox_pad, st));
+    unsigned long long* tot = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64;
     if (zc_hi >= zc_lo) {
+        // (with row marks the code array is not cleared: codes of blocks that leave early are never read)
+        if (!vol->d_rows) B2R_CUDA(cudaMemsetAsync(code, 0, nvox_pad, st));
         dim3 block(64, 4), grid(cdiv(R, 64), cdiv(R, 4), cdiv(zc_hi - zc_lo + 1, MC_ZCHUNK));
-        mc_classify_kernel<<<grid, block, 0, st>>>((const float2*)vol->d_tsdfw, code, row_active, R, zb, zc_lo, zc_hi);
+        mc_classify_kernel<<<grid, block, 0, st>>>((const float2*)vol->d_tsdfw, code, row_active, R, zb, zc_lo, zc_hi,
+                                                   (const uint8_t*)vol->d_rows);
         B2R_LAUNCH_CHECK(ctx);
     }
-    unsigned long long* tot = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64;
     // live virtual blocks -> list (device-side count in tot[2]); dead blocks keep zero totals
     if (ctx->mc_live.ensure((size_t)nblocks * 3 * sizeof(uint32_t))) return -102;
     uint32_t* live = (uint32_t*)ctx->mc_live.ptr;

@@ -91,6 +91,8 @@ int b2r_volume_import(b2r_ctx* ctx, const b2r_volume* vol, const float* d_tsdf_i
     volume_import_kernel<<<cdiv(n, 256), 256, 0, S(stream)>>>((float2*)vol->d_tsdfw, (uint32_t*)vol->d_color, R, nz,
                                                               vol->color_type, d_tsdf_in, d_weight_in, d_color_in);
     B2R_LAUNCH_CHECK(ctx);
+    if (vol->d_rows)     // imported content: every owned row may hold weights (halo rows keep what they had)
+        B2R_CUDA(cudaMemsetAsync((char*)vol->d_rows + (size_t)B2R_PAD_LO * R, 1, (size_t)nz * R, S(stream)));
     return 0;
 }
 

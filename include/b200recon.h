@@ -54,6 +54,10 @@ typedef struct b2r_volume {
     double origin[3];
     void* d_tsdfw;             /* float2 [(z_end-z_begin+PAD_LO+PAD_HI) * R * R] */
     void* d_color;             /* uint32, same count; NULL when color_type == 0 */
+    void* d_rows;              /* optional uint8 [(z_end-z_begin+PAD_LO+PAD_HI) * R]: 1 = row (plane, x) may hold a voxel
+                                * with weight != 0.  Maintained by the library (integrate marks, reset clears, import
+                                * sets all); halo planes travel with the volume's halo planes.  Extraction classifies
+                                * only cube rows next to a marked row; NULL = no information, every row is read. */
 } b2r_volume;
 
 /* ---- library / context ------------------------------------------------------------------ */
