@@ -527,6 +527,13 @@ def run_gpu(args):
             icp["pairs_per_s"] = args.icp_pairs / (icp["ms"] * 1e-3)
             icp["distribution"] = "pair p -> GPU p %% %d, no collective" % world
             extra[key] = icp
+        if world >= 8 and args.workload == "tsdf1024":      # BASELINE configs[4] on the same 8 GPUs (every rank calls it)
+            del vol
+            torch.cuda.empty_cache()
+            try:
+                extra["tsdf2048"] = bench_extra.tsdf2048_bench(rank, world, local)
+            except Exception as e:
+                extra["tsdf2048"] = {"error": repr(e)}
         if world == 1 and R <= 1024:
             try:
                 extra["scalable"] = bench_extra.scalable_bench(1024, 64, 0.9)

@@ -144,6 +144,73 @@ def sharded_mesh_bench(vol, ranges, voxel_length):
     return out
 
 
+def tsdf2048_bench(rank, world, device, steps=64, n_frames=32):
+    """BASELINE configs[4] in the driver's own record (the driver only runs the default workload): 1280x720 frames into a
+    2048^3 TSDF+colour cube (4.096 m @ 2 mm, 103 GB) z-slab sharded over the `world` ranks of this run.  Slab boundaries:
+    the coarse work probe + two feedback steps on per-frame time, like the main workload.  Frames resident in HBM,
+    CUDA-event time of `steps` integrate calls, max over ranks; every rank must call it."""
+    import torch
+    import torch.distributed as dist
+    import b200recon as o3d
+    from b200recon import parallel, runtime, synthetic as syn, _lib
+    import bench
+    wl = "tsdf2048"
+    K = bench.camera(wl)
+    R, L, trunc, poses = bench.orbit(wl)
+    intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], K["fx"], K["fy"], K["cx"], K["cy"])
+    ctx = runtime.ctx(device)
+    dev = ctx.tdev
+    frames = []
+    for p in poses[:: max(1, len(poses) // n_frames)][:n_frames]:
+        d16, rgb = syn.render_frame(p, K)
+        d = torch.empty((K["height"], K["width"]), dtype=torch.float32, device=dev)
+        _lib.check(_lib.load().b2r_depth_to_float(ctx.handle, runtime.ptr(d16), 1, K["height"], K["width"], 1000.0, 3.0,
+                                                  runtime.ptr(d), ctx.stream()))
+        frames.append((d, rgb.contiguous(), syn.extrinsic_from_pose(p)))
+    origin = syn.volume_origin(L)
+    RGB8 = o3d.pipelines.integration.TSDFVolumeColorType.RGB8
+    work = parallel.probe_plane_work(L, R, trunc, origin, [(d, e) for d, _, e in frames[::2]], intr, probe_resolution=128,
+                                     device=device)
+    ranges = parallel.balanced_slab_ranges(work, world)
+
+    def per_frame_ms(v, n):
+        for f in frames[:3]:
+            v.integrate_device(f[0], f[1], intr, f[2])
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:
+            dist.barrier()
+        e0.record()
+        for i in range(n):
+            f = frames[i % len(frames)]
+            v.integrate_device(f[0], f[1], intr, f[2])
+        ctx.join()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return e0.elapsed_time(e1) / n
+
+    for _ in range(2 if world > 1 else 0):
+        v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, RGB8, origin, z_range=ranges[rank], device=device)
+        tt = torch.zeros(world, dtype=torch.float64, device=dev)
+        tt[rank] = per_frame_ms(v, len(frames))
+        dist.all_reduce(tt)
+        ranges = parallel.rebalance_slab_ranges(ranges, work, tt.cpu().numpy())
+        del v
+        torch.cuda.empty_cache()
+    parallel.check_same_ranges(ranges, R, device=dev)
+    v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, RGB8, origin, z_range=ranges[rank], device=device)
+    ms = per_frame_ms(v, steps)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    del v
+    torch.cuda.empty_cache()
+    return {"workload": "tsdf2048: 1280x720 frames into a 2048^3 TSDF+colour cube (4.096 m @ 2 mm, 103 GB), z-slab x%d" % world,
+            "frames_per_s": 1000.0 / ms, "ms_per_step": ms, "steps": steps, "slab_boundaries": [a for a, _ in ranges] + [R],
+            "frames": "%d resident frames of the 1000-frame orbit, cycled" % len(frames)}
+
+
 BANANA_PLY = os.path.join(ROOT, "tests", "golden", "banana_poisson_nontextured.ply")
 
 
