@@ -491,7 +491,7 @@ class LocalSlabs:
 
     def import_arrays(self, tsdf, weight, color=None):
         for v, (a, b) in zip(self.slabs, self.x_ranges):
-            v.import_arrays(tsdf[:, :, a:b], weight[:, :, a:b], None if color is None else color[:, :, a:b])
+            v.import_arrays(tsdf[a:b], weight[a:b], None if color is None else color[a:b])
         self._halo_valid = False
 
     def exchange_halos(self):
