@@ -21,7 +21,7 @@ class Intrinsic(C.Structure):
 
 
 class Volume(C.Structure):
-    _fields_ = [("resolution", C.c_int32), ("z_begin", C.c_int32), ("z_end", C.c_int32), ("color_type", C.c_int32),
+    _fields_ = [("resolution", C.c_int32), ("x_begin", C.c_int32), ("x_end", C.c_int32), ("color_type", C.c_int32),
                 ("voxel_length", C.c_double), ("sdf_trunc", C.c_double), ("origin", C.c_double * 3),
                 ("d_tsdfw", c_vp), ("d_color", c_vp), ("d_rows", c_vp)]
 

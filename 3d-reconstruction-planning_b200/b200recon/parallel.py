@@ -1,6 +1,9 @@
 """Multi-GPU layer: one process per GPU, `torch.distributed` for the plumbing.
 
-  * `SlabVolume`     -- a dense R^3 TSDF cube sharded into z-slabs, one per rank.  Every rank integrates
+  * `SlabVolume`     -- a dense R^3 TSDF cube sharded into slabs of x planes (the cube is stored x-slowest, so a
+                        slab and its halo planes are contiguous, and a slab owns WHOLE (x, y) columns: Open3D's
+                        float32 z-chain and the per-column planning of a frame run once per column whatever the number
+                        of ranks), one per rank.  Every rank integrates
                         every frame into its own slab: NO data-path collective during integration (the
                         float32 z-chain of each slab starts with the replay of the planes below it, so every
                         slab is bit-identical to the single-GPU volume).
@@ -34,7 +37,7 @@ def world_info(group=None):
 
 
 def slab_range(resolution, rank, world):
-    """Planes [z_begin, z_end) owned by `rank`: contiguous, balanced to within one plane."""
+    """Planes [x_begin, x_end) owned by `rank`: contiguous, balanced to within one plane."""
     R = int(resolution)
     return R * rank // world, R * (rank + 1) // world
 
@@ -47,7 +50,7 @@ def balanced_slab_ranges(plane_work, world, min_planes=4):
     """Contiguous z-slabs with (nearly) equal WORK instead of equal plane counts.  Integration only touches the
     voxels between the cameras and the surfaces, which on a table-top orbit is the lower part of the cube: equal
     slabs leave most ranks idle.  `plane_work[z]` = expected voxel updates per frame sequence in plane z (see
-    `probe_plane_work`); returns [(z_begin, z_end)] per rank, every slab at least `min_planes` thick (halo)."""
+    `probe_plane_work`); returns [(x_begin, x_end)] per rank, every slab at least `min_planes` thick (halo)."""
     w = np.asarray(plane_work, np.float64).reshape(-1)
     R = len(w)
     if world * min_planes > R:
@@ -128,7 +131,7 @@ def profile_plane_cost(length, resolution, sdf_trunc, origin, frames, intrinsic,
     times, slabs = [], []
     for a in range(0, R, chunk):
         b = min(R, a + chunk)
-        v = integration.UniformTSDFVolume(length, R, sdf_trunc, ct, origin, z_range=(a, b), device=device)
+        v = integration.UniformTSDFVolume(length, R, sdf_trunc, ct, origin, x_range=(a, b), device=device)
         v.integrate_device(frames[0][0], frames[0][1], intrinsic, frames[0][2])       # warm-up (scratch allocation)
         c.kernel_timing(True)
         for d, col, ext in frames:
@@ -160,7 +163,7 @@ def probe_plane_work(length, resolution, sdf_trunc, origin, frames, intrinsic, p
     for depth_f32, ext in frames:
         vol.integrate_device(depth_f32, None, intrinsic, ext)
     _, w, _ = vol.export_arrays()                    # [x, y, z]
-    per_plane = np.asarray(w, np.float64).sum(axis=(0, 1))
+    per_plane = np.asarray(w, np.float64).sum(axis=(1, 2))      # [x, y, z] -> work per x plane (the slab axis)
     rep = int(np.ceil(resolution / Rp))
     return np.repeat(per_plane, rep)[: int(resolution)] / rep
 
@@ -170,7 +173,7 @@ def probe_plane_work(length, resolution, sdf_trunc, origin, frames, intrinsic, p
 # --------------------------------------------------------------------------------------------------
 def halo_plan(rank, world, n_owned, pad_lo=_lib.PAD_LO, pad_hi=_lib.PAD_HI):
     """Messages of one rank as (kind, peer, first_plane, n_planes) in units of planes of the padded slab
-    array (plane p holds z = z_begin - pad_lo + p).  `send_down` = first pad_hi owned planes -> rank-1's top
+    array (plane p holds z = x_begin - pad_lo + p).  `send_down` = first pad_hi owned planes -> rank-1's top
     pad; `send_up` = last pad_lo owned planes -> rank+1's bottom pad."""
     ops = []
     if n_owned < max(pad_lo, pad_hi) and world > 1:
@@ -279,34 +282,34 @@ class SlabVolume:
     The mesh is the single-volume mesh: same vertex and triangle sets (vertex ids are global)."""
 
     def __init__(self, length, resolution, sdf_trunc, color_type=None, origin=(0.0, 0.0, 0.0), group=None, device=None,
-                 z_ranges=None, local=None):
-        """z_ranges: optional [(z_begin, z_end)] per rank (contiguous, covering [0, resolution)), e.g. from
+                 x_ranges=None, local=None):
+        """x_ranges: optional [(x_begin, x_end)] per rank (contiguous, covering [0, resolution)), e.g. from
         `balanced_slab_ranges`; default = equal plane counts.  local: this rank's slab if it already exists (a
-        `UniformTSDFVolume(z_range=z_ranges[rank])`), else it is created here."""
+        `UniformTSDFVolume(x_range=x_ranges[rank])`), else it is created here."""
         from .pipelines import integration
         self.group = group
         self.rank, self.world = world_info(group)
         self.resolution = int(resolution)
         self.timings = {}
         ct = integration.TSDFVolumeColorType.RGB8 if color_type is None else color_type
-        if z_ranges is None:
-            z_ranges = slab_ranges(resolution, self.world)
-        z_ranges = [(int(a), int(b)) for a, b in z_ranges]
-        if (len(z_ranges) != self.world or z_ranges[0][0] != 0 or z_ranges[-1][1] != self.resolution or
-                any(z_ranges[i][1] != z_ranges[i + 1][0] for i in range(self.world - 1))):
-            raise RuntimeError("SlabVolume: z_ranges must be %d contiguous slabs covering [0, %d)" % (self.world, self.resolution))
-        self.z_begin, self.z_end = z_ranges[self.rank]
-        if self.world > 1 and (self.z_end - self.z_begin) < max(_lib.PAD_LO, _lib.PAD_HI):
+        if x_ranges is None:
+            x_ranges = slab_ranges(resolution, self.world)
+        x_ranges = [(int(a), int(b)) for a, b in x_ranges]
+        if (len(x_ranges) != self.world or x_ranges[0][0] != 0 or x_ranges[-1][1] != self.resolution or
+                any(x_ranges[i][1] != x_ranges[i + 1][0] for i in range(self.world - 1))):
+            raise RuntimeError("SlabVolume: x_ranges must be %d contiguous slabs covering [0, %d)" % (self.world, self.resolution))
+        self.x_begin, self.x_end = x_ranges[self.rank]
+        if self.world > 1 and (self.x_end - self.x_begin) < max(_lib.PAD_LO, _lib.PAD_HI):
             raise RuntimeError("SlabVolume: %d planes over %d ranks leaves slabs thinner than the halo" %
                                (self.resolution, self.world))
         if local is not None:
-            if (local.z_begin, local.z_end, local.resolution) != (self.z_begin, self.z_end, self.resolution):
+            if (local.x_begin, local.x_end, local.resolution) != (self.x_begin, self.x_end, self.resolution):
                 raise RuntimeError("SlabVolume: `local` is slab [%d,%d) of %d, this rank owns [%d,%d) of %d" % (
-                    local.z_begin, local.z_end, local.resolution, self.z_begin, self.z_end, self.resolution))
+                    local.x_begin, local.x_end, local.resolution, self.x_begin, self.x_end, self.resolution))
             self.local = local
         else:
             self.local = integration.UniformTSDFVolume(length, resolution, sdf_trunc, ct, origin,
-                                                       z_range=(self.z_begin, self.z_end), device=device)
+                                                       x_range=(self.x_begin, self.x_end), device=device)
         self._halo_valid = False
 
     def _timed(self, key, fn):
@@ -347,7 +350,7 @@ class SlabVolume:
         """One-plane-below / two-planes-above halo of {tsdf, weight} and colour from the neighbour slabs."""
         if not self._halo_valid:
             self.local._ctx.join()   # the planes are sent straight from the volume's tensors
-            exchange_halos([self.local._tsdfw, self.local._color, self.local._rows], self.z_end - self.z_begin, self.rank, self.world,
+            exchange_halos([self.local._tsdfw, self.local._color, self.local._rows], self.x_end - self.x_begin, self.rank, self.world,
                            self.group)
             self._halo_valid = True
 
@@ -443,24 +446,24 @@ class LocalSlabs:
     single-volume mesh / point cloud.  Uses: cubes cut into slabs that are extracted one after the other with a
     bounded scratch footprint, and the seam logic under test on a single GPU (tests/test_slab_seam_gpu.py)."""
 
-    def __init__(self, length, resolution, sdf_trunc, color_type=None, origin=(0.0, 0.0, 0.0), z_ranges=None,
+    def __init__(self, length, resolution, sdf_trunc, color_type=None, origin=(0.0, 0.0, 0.0), x_ranges=None,
                  n_slabs=2, device=None):
         from . import runtime
         from .pipelines import integration
         self.resolution = int(resolution)
         ct = integration.TSDFVolumeColorType.RGB8 if color_type is None else color_type
-        if z_ranges is None:
-            z_ranges = slab_ranges(resolution, n_slabs)
-        z_ranges = [(int(a), int(b)) for a, b in z_ranges]
-        n = len(z_ranges)
-        if (z_ranges[0][0] != 0 or z_ranges[-1][1] != self.resolution or
-                any(z_ranges[i][1] != z_ranges[i + 1][0] for i in range(n - 1))):
-            raise RuntimeError("LocalSlabs: z_ranges must be contiguous slabs covering [0, %d)" % self.resolution)
-        if n > 1 and min(b - a for a, b in z_ranges) < max(_lib.PAD_LO, _lib.PAD_HI):
+        if x_ranges is None:
+            x_ranges = slab_ranges(resolution, n_slabs)
+        x_ranges = [(int(a), int(b)) for a, b in x_ranges]
+        n = len(x_ranges)
+        if (x_ranges[0][0] != 0 or x_ranges[-1][1] != self.resolution or
+                any(x_ranges[i][1] != x_ranges[i + 1][0] for i in range(n - 1))):
+            raise RuntimeError("LocalSlabs: x_ranges must be contiguous slabs covering [0, %d)" % self.resolution)
+        if n > 1 and min(b - a for a, b in x_ranges) < max(_lib.PAD_LO, _lib.PAD_HI):
             raise RuntimeError("LocalSlabs: a slab is thinner than the halo (%d planes)" % max(_lib.PAD_LO, _lib.PAD_HI))
-        self.z_ranges = z_ranges
-        self.slabs = [integration.UniformTSDFVolume(length, resolution, sdf_trunc, ct, origin, z_range=zr, device=device,
-                                                    context=runtime.new_context(device)) for zr in z_ranges]
+        self.x_ranges = x_ranges
+        self.slabs = [integration.UniformTSDFVolume(length, resolution, sdf_trunc, ct, origin, x_range=zr, device=device,
+                                                    context=runtime.new_context(device)) for zr in x_ranges]
         self._halo_valid = False
 
     def __len__(self):
@@ -487,8 +490,8 @@ class LocalSlabs:
         self._halo_valid = False
 
     def import_arrays(self, tsdf, weight, color=None):
-        for v, (a, b) in zip(self.slabs, self.z_ranges):
-            v.import_arrays(tsdf[:, :, a:b], weight[:, :, a:b], None if color is None else color[:, :, a:b])
+        for v, (a, b) in zip(self.slabs, self.x_ranges):
+            v.import_arrays(tsdf[a:b], weight[a:b], None if color is None else color[a:b])
         self._halo_valid = False
 
     def exchange_halos(self):
@@ -501,7 +504,7 @@ class LocalSlabs:
             v._ctx.join()
         for k in range(len(self.slabs) - 1):
             a, b = self.slabs[k], self.slabs[k + 1]
-            na = a.z_end - a.z_begin
+            na = a.x_end - a.x_begin
             for ta, tb in ((a._tsdfw, b._tsdfw), (a._color, b._color), (a._rows, b._rows)):
                 if ta is None:
                     continue

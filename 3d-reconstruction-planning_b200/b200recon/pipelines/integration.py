@@ -5,7 +5,7 @@ A.3/A.4, rows a5/a6/f4).
     vol.integrate(rgbd, intrinsic, extrinsic)
     mesh = vol.extract_triangle_mesh();  pcd = vol.extract_point_cloud()
 
-Multi-GPU: pass `z_range=(z_begin, z_end)` to own one z-slab of the cube; `parallel.SlabVolume` wires
+Multi-GPU: pass `x_range=(x_begin, x_end)` to own one z-slab of the cube; `parallel.SlabVolume` wires
 the slabs of all ranks together (halo exchange + gather over NCCL).
 """
 import ctypes as C
@@ -28,8 +28,8 @@ class TSDFVolume:
 
 class UniformTSDFVolume(TSDFVolume):
     def __init__(self, length, resolution, sdf_trunc, color_type=TSDFVolumeColorType.RGB8, origin=(0.0, 0.0, 0.0),
-                 z_range=None, device=None, context=None):
-        """`z_range` / `device` / `context` are extensions (multi-GPU slabs, several slabs in one process)."""
+                 x_range=None, device=None, context=None):
+        """`x_range` / `device` / `context` are extensions (multi-GPU slabs, several slabs in one process)."""
         self.length = float(length)
         self.resolution = int(resolution)
         self.sdf_trunc = float(sdf_trunc)
@@ -38,10 +38,10 @@ class UniformTSDFVolume(TSDFVolume):
         self.voxel_length = self.length / self.resolution
         if self.resolution <= 0 or self.length <= 0 or self.sdf_trunc <= 0:
             raise RuntimeError("UniformTSDFVolume: length, resolution and sdf_trunc must be positive")
-        zb, ze = (0, self.resolution) if z_range is None else (int(z_range[0]), int(z_range[1]))
+        zb, ze = (0, self.resolution) if x_range is None else (int(x_range[0]), int(x_range[1]))
         if not (0 <= zb <= ze <= self.resolution):
-            raise RuntimeError("UniformTSDFVolume: bad z_range %r" % (z_range,))
-        self.z_begin, self.z_end = zb, ze
+            raise RuntimeError("UniformTSDFVolume: bad x_range %r" % (x_range,))
+        self.x_begin, self.x_end = zb, ze
         self._ctx = context if context is not None else runtime.ctx(device)
         t = runtime.torch()
         R = self.resolution
@@ -221,13 +221,14 @@ class UniformTSDFVolume(TSDFVolume):
 
     # ------------------------------------------------------------------ raw access (tests, persistence)
     def export_arrays(self):
-        """(tsdf, weight, color) as numpy in Open3D order [x, y, z_local]; colour [.., 3] in 0..255 or None."""
+        """(tsdf, weight, color) as numpy in Open3D order [x_local, y, z] (the slab's x planes); colour [.., 3] in
+        0..255 or None."""
         c = self._ctx
         t = runtime.torch()
-        R, nz = self.resolution, self.z_end - self.z_begin
-        ts = t.empty((R, R, nz), dtype=t.float32, device=c.tdev)
-        w = t.empty((R, R, nz), dtype=t.float32, device=c.tdev)
-        col = t.empty((R, R, nz, 3), dtype=t.float32, device=c.tdev) if self._color is not None else None
+        R, nx = self.resolution, self.x_end - self.x_begin
+        ts = t.empty((nx, R, R), dtype=t.float32, device=c.tdev)
+        w = t.empty((nx, R, R), dtype=t.float32, device=c.tdev)
+        col = t.empty((nx, R, R, 3), dtype=t.float32, device=c.tdev) if self._color is not None else None
         _lib.check(_lib.load().b2r_volume_export(c.handle, C.byref(self._desc), runtime.ptr(ts), runtime.ptr(w),
                                                  runtime.ptr(col), c.stream()))
         return ts.cpu().numpy(), w.cpu().numpy(), (None if col is None else col.cpu().numpy())
@@ -235,10 +236,10 @@ class UniformTSDFVolume(TSDFVolume):
     def import_arrays(self, tsdf, weight, color=None):
         c = self._ctx
         t = runtime.torch()
-        R, nz = self.resolution, self.z_end - self.z_begin
-        ts = runtime.to_device(np.ascontiguousarray(tsdf, np.float32).reshape(R, R, nz))
-        w = runtime.to_device(np.ascontiguousarray(weight, np.float32).reshape(R, R, nz))
-        col = None if color is None else runtime.to_device(np.ascontiguousarray(color, np.float32).reshape(R, R, nz, 3))
+        R, nx = self.resolution, self.x_end - self.x_begin
+        ts = runtime.to_device(np.ascontiguousarray(tsdf, np.float32).reshape(nx, R, R))
+        w = runtime.to_device(np.ascontiguousarray(weight, np.float32).reshape(nx, R, R))
+        col = None if color is None else runtime.to_device(np.ascontiguousarray(color, np.float32).reshape(nx, R, R, 3))
         _lib.check(_lib.load().b2r_volume_import(c.handle, C.byref(self._desc), runtime.ptr(ts), runtime.ptr(w),
                                                  runtime.ptr(col), c.stream()))
         c.sync()
@@ -248,14 +249,14 @@ class UniformTSDFVolume(TSDFVolume):
         ts, w, col = self.export_arrays()
         np.savez(path, tsdf=ts, weight=w, color=(np.zeros(0) if col is None else col), length=self.length,
                  resolution=self.resolution, sdf_trunc=self.sdf_trunc, color_type=int(self.color_type),
-                 origin=self.origin, z_range=np.array([self.z_begin, self.z_end]))
+                 origin=self.origin, x_range=np.array([self.x_begin, self.x_end]))
 
     @staticmethod
     def load(path, device=None):
         d = np.load(path)
         v = UniformTSDFVolume(float(d["length"]), int(d["resolution"]), float(d["sdf_trunc"]),
                               TSDFVolumeColorType(int(d["color_type"])), d["origin"],
-                              z_range=tuple(int(x) for x in d["z_range"]), device=device)
+                              x_range=tuple(int(x) for x in d["x_range"]), device=device)
         v.import_arrays(d["tsdf"], d["weight"], d["color"] if d["color"].size else None)
         return v
 

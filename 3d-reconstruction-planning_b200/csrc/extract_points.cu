@@ -11,7 +11,7 @@ namespace b2r {
 constexpr int PC_THREADS = 256;
 
 struct PcGeom {
-    int R, z_begin, z_end;
+    int R, x_begin, x_end;
     double vl, ox, oy, oz;
     int color_type;
     // ScalableTSDFVolume mode (unit_res > 0): Open3D computes positions from the unit's own origin + in-unit index
@@ -21,8 +21,8 @@ struct PcGeom {
     const int* unit_stamp;
 };
 
-__device__ __forceinline__ int64_t pidx(int R, int z_begin, int x, int y, int z) {
-    return ((int64_t)(z - z_begin + B2R_PAD_LO) * R + x) * R + y;
+__device__ __forceinline__ int64_t pidx(int R, int x_begin, int x, int y, int z) {
+    return ((int64_t)(x - x_begin + B2R_PAD_LO) * R + z) * R + y;      // x-slowest, then z, y fastest
 }
 __device__ __forceinline__ bool pc_valid(const float2 q) { return q.y != 0.0f && q.x < 0.98f && q.x >= -0.98f; }
 
@@ -30,13 +30,13 @@ __device__ __forceinline__ bool pc_valid(const float2 q) { return q.y != 0.0f &&
 __device__ __forceinline__ unsigned pc_flags(const float2* __restrict__ tsdfw, const PcGeom& G, int x, int y, int z) {
     const int R = G.R;
     if (x < 1 || y < 1 || z < 1 || x > R - 2 || y > R - 2 || z > R - 2) return 0u;
-    const int64_t i0 = pidx(R, G.z_begin, x, y, z);
+    const int64_t i0 = pidx(R, G.x_begin, x, y, z);
     const float2 q0 = __ldg(&tsdfw[i0]);
     if (!pc_valid(q0)) return 0u;
     unsigned f = 0;
-    if (x + 1 < R - 1) { const float2 q = __ldg(&tsdfw[i0 + R]); if (pc_valid(q) && q0.x * q.x < 0.0f) f |= 1u; }
+    if (x + 1 < R - 1) { const float2 q = __ldg(&tsdfw[i0 + (int64_t)R * R]); if (pc_valid(q) && q0.x * q.x < 0.0f) f |= 1u; }
     if (y + 1 < R - 1) { const float2 q = __ldg(&tsdfw[i0 + 1]); if (pc_valid(q) && q0.x * q.x < 0.0f) f |= 2u; }
-    if (z + 1 < R - 1) { const float2 q = __ldg(&tsdfw[i0 + (int64_t)R * R]); if (pc_valid(q) && q0.x * q.x < 0.0f) f |= 4u; }
+    if (z + 1 < R - 1) { const float2 q = __ldg(&tsdfw[i0 + R]); if (pc_valid(q) && q0.x * q.x < 0.0f) f |= 4u; }
     return f;
 }
 
@@ -45,11 +45,11 @@ __global__ void __launch_bounds__(PC_THREADS) pc_count_kernel(const float2* __re
                                                               uint32_t* __restrict__ blk_counts) {
     __shared__ uint32_t s_c[PC_THREADS / 32];
     const int R = G.R;
-    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int64_t n = (int64_t)(G.x_end - G.x_begin) * R * R;
     const int64_t t = (int64_t)blockIdx.x * PC_THREADS + threadIdx.x;
     unsigned c = 0;
     if (t < n) {
-        const int y = (int)(t % R), x = (int)((t / R) % R), z = G.z_begin + (int)(t / ((int64_t)R * R));
+        const int y = (int)(t % R), z = (int)((t / R) % R), x = G.x_begin + (int)(t / ((int64_t)R * R));
         c = __popc(pc_flags(tsdfw, G, x, y, z));
     }
 #pragma unroll
@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(PC_THREADS) pc_count2_kernel(const float2* __r
                                                                uint32_t* __restrict__ blk_counts, int n_count_blocks) {
     __shared__ uint32_t s_c[PC_THREADS / 32];
     const int R = G.R;
-    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int64_t n = (int64_t)(G.x_end - G.x_begin) * R * R;
     const int64_t t = ((int64_t)blockIdx.x * PC_THREADS + threadIdx.x) * 2;
     unsigned c = 0;
     if (t < n) {
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(PC_THREADS) pc_count2_kernel(const float2* __r
         const float4 q = __ldcs(reinterpret_cast<const float4*>(tsdfw + (int64_t)B2R_PAD_LO * R * R + t));
         const bool va = pc_valid(make_float2(q.x, q.y)), vb = pc_valid(make_float2(q.z, q.w));
         if (va | vb) {
-            const int y = (int)(t % R), x = (int)((t / R) % R), z = G.z_begin + (int)(t / ((int64_t)R * R));
+            const int y = (int)(t % R), z = (int)((t / R) % R), x = G.x_begin + (int)(t / ((int64_t)R * R));
             if (va) c += __popc(pc_flags(tsdfw, G, x, y, z));
             if (vb) c += __popc(pc_flags(tsdfw, G, x, y + 1, z));
         }
@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(256) pc_count_rows_kernel(const float2* __rest
                                                             uint32_t* __restrict__ blk_counts, int n_count_blocks,
                                                             const uint8_t* __restrict__ rows) {
     const int R = G.R, lane = threadIdx.x & 31;
-    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int64_t n = (int64_t)(G.x_end - G.x_begin) * R * R;
     const int nwarps = gridDim.x * 8;
     for (int b = blockIdx.x * 8 + (threadIdx.x >> 5); b < n_count_blocks; b += nwarps) {
         const int64_t t0 = (int64_t)b * PC_THREADS, t1 = min(t0 + PC_THREADS, n) - 1;
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(256) pc_count_rows_kernel(const float2* __rest
                 const float4 q = __ldcs(reinterpret_cast<const float4*>(tsdfw + (int64_t)B2R_PAD_LO * R * R + t));
                 const bool va = pc_valid(make_float2(q.x, q.y)), vb = pc_valid(make_float2(q.z, q.w));
                 if (va | vb) {
-                    const int y = (int)(t % R), x = (int)((t / R) % R), z = G.z_begin + (int)(t / ((int64_t)R * R));
+                    const int y = (int)(t % R), z = (int)((t / R) % R), x = G.x_begin + (int)(t / ((int64_t)R * R));
                     if (va) c += __popc(pc_flags(tsdfw, G, x, y, z));
                     if (vb) c += __popc(pc_flags(tsdfw, G, x, y + 1, z));
                 }
@@ -157,8 +157,8 @@ __device__ __forceinline__ double tsdf_at(const float2* __restrict__ tsdfw, cons
         r[k] = g - (double)idx[k];
     }
     const int R = G.R;
-    const int64_t b = pidx(R, G.z_begin, idx[0], idx[1], idx[2]);
-    const int64_t sx = R, sy = 1, sz = (int64_t)R * R;
+    const int64_t b = pidx(R, G.x_begin, idx[0], idx[1], idx[2]);
+    const int64_t sx = (int64_t)R * R, sy = 1, sz = R;
     const double t000 = (double)__ldg(&tsdfw[b]).x, t001 = (double)__ldg(&tsdfw[b + sz]).x;
     const double t010 = (double)__ldg(&tsdfw[b + sy]).x, t011 = (double)__ldg(&tsdfw[b + sy + sz]).x;
     const double t100 = (double)__ldg(&tsdfw[b + sx]).x, t101 = (double)__ldg(&tsdfw[b + sx + sz]).x;
@@ -191,7 +191,7 @@ __device__ __forceinline__ double tsdf_at_units(const float2* __restrict__ tsdfw
     auto T = [&](int dx, int dy, int dz) -> double {
         const int x = idx[0] + dx, y = idx[1] + dy, z = idx[2] + dz;
         if (x >= R || y >= R || z >= R) return 0.0;      // the neighbouring unit lies outside the cube: missing
-        return (double)__ldg(&tsdfw[pidx(R, G.z_begin, x, y, z)]).x;
+        return (double)__ldg(&tsdfw[pidx(R, G.x_begin, x, y, z)]).x;
     };
     return (1 - r[0]) * ((1 - r[1]) * ((1 - r[2]) * T(0, 0, 0) + r[2] * T(0, 0, 1)) + r[1] * ((1 - r[2]) * T(0, 1, 0) + r[2] * T(0, 1, 1))) +
            r[0] * ((1 - r[1]) * ((1 - r[2]) * T(1, 0, 0) + r[2] * T(1, 0, 1)) + r[1] * ((1 - r[2]) * T(1, 1, 0) + r[2] * T(1, 1, 1)));
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
                                                              double* __restrict__ cols) {
     __shared__ uint32_t smem[33];
     const int R = G.R;
-    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int64_t n = (int64_t)(G.x_end - G.x_begin) * R * R;
     const unsigned nl = (unsigned)*n_live;
     for (unsigned li = blockIdx.x; li < nl; li += gridDim.x) {
     const unsigned vb = live_list[li];
@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
     unsigned f = 0;
     int x = 0, y = 0, z = 0;
     if (t < n) {
-        y = (int)(t % R); x = (int)((t / R) % R); z = G.z_begin + (int)(t / ((int64_t)R * R));
+        y = (int)(t % R); z = (int)((t / R) % R); x = G.x_begin + (int)(t / ((int64_t)R * R));
         f = pc_flags(tsdfw, G, x, y, z);
     }
     uint32_t total;
@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
     if (total == 0 || f == 0) continue;
     int64_t k = (int64_t)blk_off[vb] + local;
     const double hvl = 0.5 * G.vl;
-    const int64_t i0 = pidx(R, G.z_begin, x, y, z);
+    const int64_t i0 = pidx(R, G.x_begin, x, y, z);
     const float f0 = tsdfw[i0].x;
     double p0[3] = {hvl + G.vl * (double)x, hvl + G.vl * (double)y, hvl + G.vl * (double)z};
     if (UNITS) {     // (hvl + vl * in-unit index) + index.cast<double>() * unit_length, world coordinates
@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(PC_THREADS) pc_emit_kernel(const float2* __res
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
         if (!(f & (1u << a))) continue;
-        const int64_t i1 = i0 + (a == 0 ? (int64_t)R : a == 1 ? (int64_t)1 : (int64_t)R * R);
+        const int64_t i1 = i0 + (a == 0 ? (int64_t)R * R : a == 1 ? (int64_t)1 : (int64_t)R);      // +x, +y, +z
         const float f1 = tsdfw[i1].x;
         const float r0 = fabsf(f0), r1 = fabsf(f1);
         double p[3] = {p0[0], p0[1], p0[2]};
@@ -292,7 +292,7 @@ int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_poi
     B2R_CUDA(cudaSetDevice(ctx->device));
     B2R_CUDA(join_side(ctx, S(stream)));   // items kernels of earlier integrate calls run on the side stream
     cudaStream_t st = S(stream);
-    const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
+    const int R = vol->resolution, nz = vol->x_end - vol->x_begin;
     *n_points = 0;
     ctx->pc_n = 0;
     ctx->pc_vol = vol->d_tsdfw; ctx->pc_gen = ctx->write_gen;
@@ -304,7 +304,7 @@ int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_poi
     uint32_t* live = blk + nblocks;
     uint32_t* live_pos = blk + 2 * (size_t)nblocks;
     uint32_t* live_list = blk + 3 * (size_t)nblocks;
-    PcGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
+    PcGeom G{R, vol->x_begin, vol->x_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
              vol->color_type};
     if (vol->d_rows && R % 2 == 0 && (((uintptr_t)vol->d_tsdfw) & 15) == 0) {
         B2R_CUDA(cudaMemsetAsync(blk, 0, (size_t)nblocks * sizeof(uint32_t), st));
@@ -333,13 +333,13 @@ static int points_emit(b2r_ctx* ctx, const b2r_volume* vol, int unit_res, const 
     B2R_CUDA(cudaSetDevice(ctx->device));
     B2R_CHECK(ctx->pc_vol == vol->d_tsdfw && ctx->pc_gen == ctx->write_gen, -9,
               "b2r_extract_points_emit: the volume was written (or another volume counted) since b2r_extract_points_count; count again");
-    const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
+    const int R = vol->resolution, nz = vol->x_end - vol->x_begin;
     if (nz <= 0 || R < 3 || ctx->pc_n == 0) return 0;
     B2R_CHECK(d_points && d_normals, -1, "b2r_extract_points_emit: NULL output");
     const int64_t n = (int64_t)nz * R * R;
     const int nblocks = cdiv(n, PC_THREADS);
     PcGeom G;
-    G.R = R; G.z_begin = vol->z_begin; G.z_end = vol->z_end; G.vl = vol->voxel_length;
+    G.R = R; G.x_begin = vol->x_begin; G.x_end = vol->x_end; G.vl = vol->voxel_length;
     G.ox = vol->origin[0]; G.oy = vol->origin[1]; G.oz = vol->origin[2]; G.color_type = vol->color_type;
     G.unit_res = unit_res; G.nu = unit_res ? R / unit_res : 0; G.unit_len = vol->voxel_length * unit_res;
     for (int a = 0; a < 3; ++a) G.uoff[a] = unit_offset ? unit_offset[a] : 0;
@@ -367,7 +367,7 @@ int b2r_extract_points_emit_units(b2r_ctx* ctx, const b2r_volume* vol, int unit_
                                   const int32_t* d_unit_stamp, double* d_points, double* d_normals, double* d_colors,
                                   void* stream) {
     B2R_CHECK(ctx && vol && vol->d_tsdfw && unit_offset && d_unit_stamp, -1, "b2r_extract_points_emit_units: NULL argument");
-    B2R_CHECK(unit_resolution >= 1 && vol->resolution % unit_resolution == 0 && vol->z_begin == 0 && vol->z_end == vol->resolution,
+    B2R_CHECK(unit_resolution >= 1 && vol->resolution % unit_resolution == 0 && vol->x_begin == 0 && vol->x_end == vol->resolution,
               -6, "b2r_extract_points_emit_units: whole cube of whole units expected");
     return points_emit(ctx, vol, unit_resolution, unit_offset, d_unit_stamp, d_points, d_normals, d_colors, stream);
 }

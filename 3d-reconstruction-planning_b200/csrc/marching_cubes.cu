@@ -16,8 +16,8 @@
 // Vertex positions use Open3D's exact double expression, so they are bit-identical; the ORDER of
 // vertices/triangles is memory order instead of first-touch scan order.
 //
-// Slabs: a slab owns voxels (and cubes) of planes [z_begin, z_end); it reads halo planes
-// z_begin-1 and z_end (B2R_PAD_*), and the vertex-id table of plane z_end comes from the slab above
+// Slabs: a slab owns voxels (and cubes) of the x planes [x_begin, x_end) (memory is x-slowest: plane, then z, then y);
+// it reads halo planes x_begin-1 and x_end (B2R_PAD_*), and the vertex-id table of plane x_end comes from the slab above
 // through b2r_mesh_seam_buffers (one extra R*R*4-byte message).
 #include "frame.cuh"
 #include "scan.cuh"
@@ -29,79 +29,82 @@ constexpr int MC_ZCHUNK = 32;
 constexpr int MC_THREADS = 256;
 
 struct McGeom {
-    int R, z_begin, z_end;
+    int R, x_begin, x_end;
     double vl, ox, oy, oz;
     int color_type;
 };
 
-__device__ __forceinline__ int64_t vidx(int R, int z_begin, int x, int y, int z) {
-    return ((int64_t)(z - z_begin + B2R_PAD_LO) * R + x) * R + y;
+__device__ __forceinline__ int64_t vidx(int R, int x_begin, int x, int y, int z) {
+    return ((int64_t)(x - x_begin + B2R_PAD_LO) * R + z) * R + y;
 }
 
 // sign/valid nibble of the 4 corners (x,y),(x+1,y),(x+1,y+1),(x,y+1) of plane z
-__device__ __forceinline__ unsigned plane_nibble(const float2* __restrict__ tsdfw, int R, int z_begin, int x, int y,
+__device__ __forceinline__ unsigned plane_nibble(const float2* __restrict__ tsdfw, int R, int x_begin, int x, int y,
                                                  int z, bool& valid) {
-    const int64_t i = vidx(R, z_begin, x, y, z);
+    const int64_t i = vidx(R, x_begin, x, y, z);
+    const int64_t sx = (int64_t)R * R;                      // x + 1
     const float2 a = __ldg(&tsdfw[i]), d = __ldg(&tsdfw[i + 1]);
-    const float2 b = __ldg(&tsdfw[i + R]), c = __ldg(&tsdfw[i + R + 1]);
+    const float2 b = __ldg(&tsdfw[i + sx]), c = __ldg(&tsdfw[i + sx + 1]);
     valid = (a.y != 0.0f) && (b.y != 0.0f) && (c.y != 0.0f) && (d.y != 0.0f);
     return (a.x < 0.0f ? 1u : 0u) | (b.x < 0.0f ? 2u : 0u) | (c.x < 0.0f ? 4u : 0u) | (d.x < 0.0f ? 8u : 0u);
 }
 
-// grid: (ceil(R/64), ceil(R/4), nchunks); block (64, 4): threadIdx.x -> y, threadIdx.y -> x
+// grid: (ceil(R/64), ceil(cube x planes / 4), z chunks); block (64, 4): threadIdx.x -> y, threadIdx.y -> x.  A thread
+// marches its (x, y) column along z (the cube index's low / high nibble are the z and z+1 corners, so the carry runs
+// along z whatever the memory order; consecutive z are R voxels apart).
 __global__ void __launch_bounds__(256) mc_classify_kernel(const float2* __restrict__ tsdfw, uint8_t* __restrict__ code,
-                                                          uint8_t* __restrict__ row_active, int R, int z_begin, int zc_lo,
-                                                          int zc_hi, const uint8_t* __restrict__ rows) {
+                                                          uint8_t* __restrict__ row_active, int R, int x_begin, int xc_lo,
+                                                          int xc_hi, const uint8_t* __restrict__ rows) {
     const int y = blockIdx.x * 64 + threadIdx.x;
-    const int x = blockIdx.y * 4 + threadIdx.y;
-    const int z0 = zc_lo + blockIdx.z * MC_ZCHUNK;
-    const int z1 = min(z0 + MC_ZCHUNK, zc_hi + 1);  // cubes z0 .. z1-1
+    const int xb0 = xc_lo + blockIdx.y * 4;
+    const int x = xb0 + threadIdx.y;
+    const int z0 = blockIdx.z * MC_ZCHUNK;
+    const int z1 = min(z0 + MC_ZCHUNK, R - 1);  // cubes z0 .. z1-1 (no cube starts at z = R-1)
     if (rows) {
-        // Output sensitivity (b2r_volume::d_rows): a cube of row (z, x) can only be active when rows (z, x), (z+1, x),
-        // (z, x+1), (z+1, x+1) all hold weights, and its code is only ever READ next to an active cube (see mc_live), so
-        // a block none of whose (z0..z1, x..x+4) rows is marked has nothing to classify and nothing anyone will read:
-        // it leaves without touching the volume (one ~165-byte look at the marks instead of 64 KB x 33 planes).
+        // Output sensitivity (b2r_volume::d_rows): a cube of row (x, z) can only be active when rows (x, z), (x+1, z),
+        // (x, z+1), (x+1, z+1) all hold weights, and its code is only ever READ next to an active cube (see mc_live), so
+        // a block none of whose (x..x+4, z0..z1) rows is marked has nothing to classify and nothing anyone will read:
+        // it leaves without touching the volume (one ~165-byte look at the marks instead of 64 KB x 33 rows).
         const int t = threadIdx.y * 64 + threadIdx.x;
-        const int zz = z0 + t / 5, xx = blockIdx.y * 4 + t % 5;
-        const bool m = t < 5 * (z1 - z0 + 1) && xx < R && rows[(int64_t)(zz - z_begin + B2R_PAD_LO) * R + xx] != 0;
+        const int xx = xb0 + t / 33, zz = z0 + t % 33;
+        const bool m = t < 5 * 33 && xx <= xc_hi + 1 && zz <= z1 && rows[(int64_t)(xx - x_begin + B2R_PAD_LO) * R + zz] != 0;
         if (!__syncthreads_or(m)) return;
     }
-    if (x >= R || y >= R || z0 >= z1) return;
-    const bool edge = (x >= R - 1) || (y >= R - 1);
-    if (edge) {  // no cube starts on the last row/column
-        for (int z = z0; z < z1; ++z) code[vidx(R, z_begin, x, y, z)] = 0;
+    if (x > xc_hi || y >= R || z0 >= z1) return;
+    if (y >= R - 1) {  // no cube starts on the last column
+        for (int z = z0; z < z1; ++z) code[vidx(R, x_begin, x, y, z)] = 0;
         return;
     }
     bool v_lo;
-    unsigned n_lo = plane_nibble(tsdfw, R, z_begin, x, y, z0, v_lo);
+    unsigned n_lo = plane_nibble(tsdfw, R, x_begin, x, y, z0, v_lo);
     for (int z = z0; z < z1; ++z) {   // (#pragma unroll 4 was measured: 3.18 ms instead of 2.47 ms at 1024^3)
         bool v_hi;
-        const unsigned n_hi = plane_nibble(tsdfw, R, z_begin, x, y, z + 1, v_hi);
+        const unsigned n_hi = plane_nibble(tsdfw, R, x_begin, x, y, z + 1, v_hi);
         const unsigned c = n_lo | (n_hi << 4);
         const bool active = v_lo && v_hi && c != 0u && c != 255u;
-        code[vidx(R, z_begin, x, y, z)] = active ? (uint8_t)c : (uint8_t)0;
-        if (active) row_active[(int64_t)(z - z_begin + B2R_PAD_LO) * R + x] = 1;   // (z, x) row holds an active cube
+        code[vidx(R, x_begin, x, y, z)] = active ? (uint8_t)c : (uint8_t)0;
+        if (active) row_active[(int64_t)(x - x_begin + B2R_PAD_LO) * R + z] = 1;   // (x, z) row holds an active cube
         n_lo = n_hi; v_lo = v_hi;
     }
 }
 
-__device__ __forceinline__ unsigned code_at(const uint8_t* __restrict__ code, int R, int z_begin, int zc_lo, int zc_hi,
+__device__ __forceinline__ unsigned code_at(const uint8_t* __restrict__ code, int R, int x_begin, int xc_lo, int xc_hi,
                                             int x, int y, int z) {
-    if (x < 0 || y < 0 || z < zc_lo || z > zc_hi) return 0u;
-    return (unsigned)__ldg(&code[vidx(R, z_begin, x, y, z)]);
+    if (z < 0 || z > R - 2 || y < 0 || x < xc_lo || x > xc_hi) return 0u;
+    return (unsigned)__ldg(&code[vidx(R, x_begin, x, y, z)]);
 }
 __device__ __forceinline__ unsigned xbit(unsigned c, int a, int b) { return ((c >> a) ^ (c >> b)) & 1u; }
 
 // Owned-edge vertex flags (bit0 +x, bit1 +y, bit2 +z) of voxel (x,y,z).
-__device__ __forceinline__ unsigned edge_flags(const uint8_t* __restrict__ code, int R, int z_begin, int zc_lo,
-                                               int zc_hi, int x, int y, int z, unsigned& own_code) {
-    const unsigned c000 = code_at(code, R, z_begin, zc_lo, zc_hi, x, y, z);
-    const unsigned c0m0 = code_at(code, R, z_begin, zc_lo, zc_hi, x, y - 1, z);
-    const unsigned c00m = code_at(code, R, z_begin, zc_lo, zc_hi, x, y, z - 1);
-    const unsigned c0mm = code_at(code, R, z_begin, zc_lo, zc_hi, x, y - 1, z - 1);
-    const unsigned cm00 = code_at(code, R, z_begin, zc_lo, zc_hi, x - 1, y, z);
-    const unsigned cm0m = code_at(code, R, z_begin, zc_lo, zc_hi, x - 1, y, z - 1);
-    const unsigned cmm0 = code_at(code, R, z_begin, zc_lo, zc_hi, x - 1, y - 1, z);
+__device__ __forceinline__ unsigned edge_flags(const uint8_t* __restrict__ code, int R, int x_begin, int xc_lo,
+                                               int xc_hi, int x, int y, int z, unsigned& own_code) {
+    const unsigned c000 = code_at(code, R, x_begin, xc_lo, xc_hi, x, y, z);
+    const unsigned c0m0 = code_at(code, R, x_begin, xc_lo, xc_hi, x, y - 1, z);
+    const unsigned c00m = code_at(code, R, x_begin, xc_lo, xc_hi, x, y, z - 1);
+    const unsigned c0mm = code_at(code, R, x_begin, xc_lo, xc_hi, x, y - 1, z - 1);
+    const unsigned cm00 = code_at(code, R, x_begin, xc_lo, xc_hi, x - 1, y, z);
+    const unsigned cm0m = code_at(code, R, x_begin, xc_lo, xc_hi, x - 1, y, z - 1);
+    const unsigned cmm0 = code_at(code, R, x_begin, xc_lo, xc_hi, x - 1, y - 1, z);
     own_code = c000;
     const unsigned fx = xbit(c000, 0, 1) | xbit(c0m0, 3, 2) | xbit(c00m, 4, 5) | xbit(c0mm, 7, 6);
     const unsigned fy = xbit(c000, 0, 3) | xbit(cm00, 1, 2) | xbit(c00m, 4, 7) | xbit(cm0m, 5, 6);
@@ -110,8 +113,8 @@ __device__ __forceinline__ unsigned edge_flags(const uint8_t* __restrict__ code,
 }
 
 // Output sensitivity: the surface touches a tiny fraction of the cube, so the per-voxel passes below run only on
-// the "virtual blocks" (256 consecutive voxels = part of one or several (z, x) rows) that can produce anything.
-// A voxel's owned edges / triangles depend on cubes of rows (z, x), (z-1, x), (z, x-1), (z-1, x-1) only; a
+// the "virtual blocks" (256 consecutive voxels = part of one or several (x, z) rows) that can produce anything.
+// A voxel's owned edges / triangles depend on cubes of rows (x, z), (x-1, z), (x, z-1), (x-1, z-1) only; a
 // block none of whose rows has such an active cube is dead: its vert_tab entries stay unwritten (never read) and
 // its totals stay zero.  mc_live marks the live blocks, a scan + compaction turns the marks into a list, and the
 // passes are persistent kernels walking that list (launching a block per 256 voxels of a 1024^3 cube costs more
@@ -140,27 +143,27 @@ __global__ void __launch_bounds__(256) mc_live_list_kernel(const uint32_t* __res
 
 // flat thread per owned voxel (memory order).  Writes vert_tab[voxel] = flags << 29 (ids are added by
 // mc_emit_vertices) and per-block totals.
-__global__ void __launch_bounds__(MC_THREADS) mc_count_kernel(const uint8_t* __restrict__ code, int R, int z_begin,
-                                                              int z_end, int zc_lo, int zc_hi,
+__global__ void __launch_bounds__(MC_THREADS) mc_count_kernel(const uint8_t* __restrict__ code, int R, int x_begin,
+                                                              int x_end, int xc_lo, int xc_hi,
                                                               const uint32_t* __restrict__ live_list,
                                                               const unsigned long long* __restrict__ n_live,
                                                               uint32_t* __restrict__ vert_tab,
                                                               uint32_t* __restrict__ blk_verts,
                                                               uint32_t* __restrict__ blk_tris) {
     __shared__ uint32_t s_v[MC_THREADS / 32], s_t[MC_THREADS / 32];
-    const int64_t n = (int64_t)(z_end - z_begin) * R * R;
+    const int64_t n = (int64_t)(x_end - x_begin) * R * R;
     const unsigned nl = (unsigned)*n_live;
     for (unsigned li = blockIdx.x; li < nl; li += gridDim.x) {
         const unsigned vb = live_list[li];
         const int64_t t = (int64_t)vb * MC_THREADS + threadIdx.x;
         unsigned nv = 0, nt = 0;
         if (t < n) {
-            const int y = (int)(t % R), x = (int)((t / R) % R), z = z_begin + (int)(t / ((int64_t)R * R));
+            const int y = (int)(t % R), z = (int)((t / R) % R), x = x_begin + (int)(t / ((int64_t)R * R));
             unsigned own;
-            const unsigned f = edge_flags(code, R, z_begin, zc_lo, zc_hi, x, y, z, own);
+            const unsigned f = edge_flags(code, R, x_begin, xc_lo, xc_hi, x, y, z, own);
             nv = __popc(f);
             nt = d_mc_ntri_table[own];
-            vert_tab[vidx(R, z_begin, x, y, z)] = f << 29;
+            vert_tab[vidx(R, x_begin, x, y, z)] = f << 29;
         }
         // warp shuffle reduction, then one shared-memory pass per block
 #pragma unroll
@@ -203,7 +206,7 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_vertices_kernel(const floa
                                                                       double* __restrict__ vcols) {
     __shared__ uint32_t smem[33];
     const int R = G.R;
-    const int64_t n = (int64_t)(G.z_end - G.z_begin) * R * R;
+    const int64_t n = (int64_t)(G.x_end - G.x_begin) * R * R;
     const unsigned nl = (unsigned)*n_live;
     for (unsigned li = blockIdx.x; li < nl; li += gridDim.x) {
         const unsigned vb = live_list[li];
@@ -212,8 +215,8 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_vertices_kernel(const floa
         int x = 0, y = 0, z = 0;
         int64_t vi = 0;
         if (t < n) {
-            y = (int)(t % R); x = (int)((t / R) % R); z = G.z_begin + (int)(t / ((int64_t)R * R));
-            vi = vidx(R, G.z_begin, x, y, z);
+            y = (int)(t % R); z = (int)((t / R) % R); x = G.x_begin + (int)(t / ((int64_t)R * R));
+            vi = vidx(R, G.x_begin, x, y, z);
             f = vert_tab[vi] >> 29;
         }
         uint32_t total;
@@ -229,7 +232,7 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_vertices_kernel(const floa
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
             if (!(f & (1u << a))) continue;
-            const int64_t ni = vi + (a == 0 ? (int64_t)R : a == 1 ? (int64_t)1 : (int64_t)R * R);
+            const int64_t ni = vi + (a == 0 ? (int64_t)R * R : a == 1 ? (int64_t)1 : (int64_t)R);      // +x, +y, +z
             const float f1s = tsdfw[ni].x;
             const double f0 = fabs((double)f0s), f1 = fabs((double)f1s);
             double pt[3] = {hvl + G.vl * (double)x, hvl + G.vl * (double)y, hvl + G.vl * (double)z};
@@ -250,13 +253,13 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_vertices_kernel(const floa
 
 __global__ void __launch_bounds__(MC_THREADS) mc_emit_triangles_kernel(const uint8_t* __restrict__ code,
                                                                        const uint32_t* __restrict__ vert_tab, int R,
-                                                                       int z_begin, int z_end, int zc_hi,
+                                                                       int x_begin, int x_end, int xc_hi,
                                                                        const uint32_t* __restrict__ live_list,
                                                                        const unsigned long long* __restrict__ n_live,
                                                                        const uint32_t* __restrict__ blk_off,
                                                                        int32_t* __restrict__ tris) {
     __shared__ uint32_t smem[33];
-    const int64_t n = (int64_t)(z_end - z_begin) * R * R;
+    const int64_t n = (int64_t)(x_end - x_begin) * R * R;
     const unsigned nl = (unsigned)*n_live;
     for (unsigned li = blockIdx.x; li < nl; li += gridDim.x) {
         const unsigned vb = live_list[li];
@@ -264,8 +267,8 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_triangles_kernel(const uin
         unsigned c = 0;
         int x = 0, y = 0, z = 0;
         if (t < n) {
-            y = (int)(t % R); x = (int)((t / R) % R); z = z_begin + (int)(t / ((int64_t)R * R));
-            if (z <= zc_hi) c = code[vidx(R, z_begin, x, y, z)];
+            y = (int)(t % R); z = (int)((t / R) % R); x = x_begin + (int)(t / ((int64_t)R * R));
+            if (x <= xc_hi && z <= R - 2) c = code[vidx(R, x_begin, x, y, z)];
         }
         const unsigned nt = d_mc_ntri_table[c];
         uint32_t total;
@@ -279,7 +282,7 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_triangles_kernel(const uin
             if (d_mc_edge_table[c] & (1 << e)) {
                 const int ex = x + d_mc_edge_shift[e][0], ey = y + d_mc_edge_shift[e][1], ez = z + d_mc_edge_shift[e][2];
                 const int axis = d_mc_edge_shift[e][3];
-                const uint32_t ent = __ldg(&vert_tab[vidx(R, z_begin, ex, ey, ez)]);
+                const uint32_t ent = __ldg(&vert_tab[vidx(R, x_begin, ex, ey, ez)]);
                 const unsigned fl = ent >> 29;
                 ids[e] = (int)((ent & 0x1fffffffu) + __popc(fl & ((1u << axis) - 1u)));
             }
@@ -293,10 +296,10 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_triangles_kernel(const uin
     }
 }
 
-static void cube_z_range(const b2r_volume* vol, int& zc_lo, int& zc_hi) {
-    // cubes this slab must classify: its own (z in [z_begin, z_end) and z <= R-2) plus z_begin-1
-    zc_lo = vol->z_begin > 0 ? vol->z_begin - 1 : 0;
-    zc_hi = (vol->z_end - 1 < vol->resolution - 2) ? vol->z_end - 1 : vol->resolution - 2;
+static void cube_x_range(const b2r_volume* vol, int& xc_lo, int& xc_hi) {
+    // cubes this slab must classify: its own (x in [x_begin, x_end) and x <= R-2) plus x_begin-1
+    xc_lo = vol->x_begin > 0 ? vol->x_begin - 1 : 0;
+    xc_hi = (vol->x_end - 1 < vol->resolution - 2) ? vol->x_end - 1 : vol->resolution - 2;
 }
 
 }  // namespace b2r
@@ -311,7 +314,7 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
     B2R_CUDA(cudaSetDevice(ctx->device));
     B2R_CUDA(join_side(ctx, S(stream)));   // items kernels of earlier integrate calls run on the side stream
     cudaStream_t st = S(stream);
-    const int R = vol->resolution, zb = vol->z_begin, ze = vol->z_end, nz = ze - zb;
+    const int R = vol->resolution, zb = vol->x_begin, ze = vol->x_end, nz = ze - zb;
     *n_vertices = 0; *n_triangles = 0;
     ctx->mc_nv = ctx->mc_nt = 0;
     ctx->mc_R = R; ctx->mc_zb = zb; ctx->mc_ze = ze;
@@ -328,17 +331,17 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
     uint32_t* vert_tab = (uint32_t*)ctx->mc_vert_id.ptr;
     uint32_t* blk_v = (uint32_t*)ctx->mc_block_counts.ptr;
     uint32_t* blk_t = blk_v + nblocks;
-    int zc_lo, zc_hi;
-    cube_z_range(vol, zc_lo, zc_hi);
+    int xc_lo, xc_hi;
+    cube_x_range(vol, xc_lo, xc_hi);
     if (ctx->mc_flags.ensure(planes * R)) return -102;
     uint8_t* row_active = (uint8_t*)ctx->mc_flags.ptr;
     B2R_CUDA(cudaMemsetAsync(row_active, 0, planes * R, st));
     unsigned long long* tot = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64;
-    if (zc_hi >= zc_lo) {
+    if (xc_hi >= xc_lo) {
         // (with row marks the code array is not cleared: codes of blocks that leave early are never read)
         if (!vol->d_rows) B2R_CUDA(cudaMemsetAsync(code, 0, nvox_pad, st));
-        dim3 block(64, 4), grid(cdiv(R, 64), cdiv(R, 4), cdiv(zc_hi - zc_lo + 1, MC_ZCHUNK));
-        mc_classify_kernel<<<grid, block, 0, st>>>((const float2*)vol->d_tsdfw, code, row_active, R, zb, zc_lo, zc_hi,
+        dim3 block(64, 4), grid(cdiv(R, 64), cdiv(xc_hi - xc_lo + 1, 4), cdiv(R - 1, MC_ZCHUNK));
+        mc_classify_kernel<<<grid, block, 0, st>>>((const float2*)vol->d_tsdfw, code, row_active, R, zb, xc_lo, xc_hi,
                                                    (const uint8_t*)vol->d_rows);
         B2R_LAUNCH_CHECK(ctx);
     }
@@ -353,7 +356,7 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
     mc_live_list_kernel<<<cdiv(nblocks, 256), 256, 0, st>>>(live, live_pos, nblocks, live_list);
     B2R_LAUNCH_CHECK(ctx);
     B2R_CUDA(cudaMemsetAsync(blk_v, 0, (size_t)nblocks * 2 * sizeof(uint32_t), st));
-    mc_count_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, st>>>(code, R, zb, ze, zc_lo, zc_hi, live_list, (unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE, vert_tab, blk_v,
+    mc_count_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, st>>>(code, R, zb, ze, xc_lo, xc_hi, live_list, (unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE, vert_tab, blk_v,
                                                               blk_t);
     B2R_LAUNCH_CHECK(ctx);
     if (int rc = scan_exclusive_u32(ctx, blk_v, blk_v, nblocks, tot, st)) return rc;
@@ -370,7 +373,7 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
 
 static int mc_state_ok(b2r_ctx* ctx, const b2r_volume* vol, const char* who) {
     B2R_CHECK(ctx && vol && vol->d_tsdfw, -1, "%s: NULL argument", who);
-    B2R_CHECK(ctx->mc_R == vol->resolution && ctx->mc_zb == vol->z_begin && ctx->mc_ze == vol->z_end, -9,
+    B2R_CHECK(ctx->mc_R == vol->resolution && ctx->mc_zb == vol->x_begin && ctx->mc_ze == vol->x_end, -9,
               "%s: call b2r_extract_mesh_count on this volume first", who);
     B2R_CHECK(ctx->mc_vol == vol->d_tsdfw && ctx->mc_gen == ctx->write_gen, -9,
               "%s: the volume was written (or another volume counted) since b2r_extract_mesh_count; count again", who);
@@ -381,14 +384,14 @@ int b2r_extract_mesh_vertices(b2r_ctx* ctx, const b2r_volume* vol, int64_t verte
                               double* d_colors, void* stream) {
     if (int rc = mc_state_ok(ctx, vol, "b2r_extract_mesh_vertices")) return rc;
     B2R_CUDA(cudaSetDevice(ctx->device));
-    const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
+    const int R = vol->resolution, nz = vol->x_end - vol->x_begin;
     if (nz <= 0 || R < 2) return 0;
     B2R_CHECK(vertex_base >= 0 && vertex_base + ctx->mc_nv < (1ll << 29), -8,
               "b2r_extract_mesh_vertices: vertex ids exceed the 2^29 id space");
     B2R_CHECK(ctx->mc_nv == 0 || d_vertices, -1, "b2r_extract_mesh_vertices: NULL output");
     const int64_t n = (int64_t)nz * R * R;
     const int nblocks = cdiv(n, MC_THREADS);
-    McGeom G{R, vol->z_begin, vol->z_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
+    McGeom G{R, vol->x_begin, vol->x_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
              vol->color_type};
     const uint32_t* live_list = (const uint32_t*)ctx->mc_live.ptr + 2 * (size_t)nblocks;
     const unsigned long long* n_live = (const unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE;
@@ -407,7 +410,7 @@ int b2r_mesh_seam_buffers(b2r_ctx* ctx, const b2r_volume* vol, void** d_send_fir
     const int64_t plane = (int64_t)vol->resolution * vol->resolution;
     uint32_t* tab = (uint32_t*)ctx->mc_vert_id.ptr;
     if (d_send_first_plane) *d_send_first_plane = tab + plane * B2R_PAD_LO;
-    if (d_recv_top_plane) *d_recv_top_plane = tab + plane * (B2R_PAD_LO + (vol->z_end - vol->z_begin));
+    if (d_recv_top_plane) *d_recv_top_plane = tab + plane * (B2R_PAD_LO + (vol->x_end - vol->x_begin));
     if (bytes) *bytes = plane * (int64_t)sizeof(uint32_t);
     return 0;
 }
@@ -415,19 +418,19 @@ int b2r_mesh_seam_buffers(b2r_ctx* ctx, const b2r_volume* vol, void** d_send_fir
 int b2r_extract_mesh_triangles(b2r_ctx* ctx, const b2r_volume* vol, int32_t* d_triangles, void* stream) {
     if (int rc = mc_state_ok(ctx, vol, "b2r_extract_mesh_triangles")) return rc;
     B2R_CUDA(cudaSetDevice(ctx->device));
-    const int R = vol->resolution, nz = vol->z_end - vol->z_begin;
+    const int R = vol->resolution, nz = vol->x_end - vol->x_begin;
     if (nz <= 0 || R < 2 || ctx->mc_nt == 0) return 0;
     B2R_CHECK(d_triangles, -1, "b2r_extract_mesh_triangles: NULL output");
     const int64_t n = (int64_t)nz * R * R;
     const int nblocks = cdiv(n, MC_THREADS);
-    int zc_lo, zc_hi;
-    cube_z_range(vol, zc_lo, zc_hi);
+    int xc_lo, xc_hi;
+    cube_x_range(vol, xc_lo, xc_hi);
     const uint32_t* blk_t = (const uint32_t*)ctx->mc_block_counts.ptr + nblocks;
     const uint32_t* live_list = (const uint32_t*)ctx->mc_live.ptr + 2 * (size_t)nblocks;
     const unsigned long long* n_live = (const unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE;
     mc_emit_triangles_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, S(stream)>>>((const uint8_t*)ctx->mc_code.ptr,
                                                                               (const uint32_t*)ctx->mc_vert_id.ptr, R,
-                                                                              vol->z_begin, vol->z_end, zc_hi, live_list, n_live,
+                                                                              vol->x_begin, vol->x_end, xc_hi, live_list, n_live,
                                                                               blk_t, d_triangles);
     B2R_LAUNCH_CHECK(ctx);
     return 0;

@@ -11,10 +11,10 @@ __global__ void volume_export_kernel(const float2* __restrict__ tsdfw, const uin
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     const int y = (int)(t % R);
-    const int x = (int)((t / R) % R);
-    const int zl = (int)(t / ((int64_t)R * R));
-    const int64_t in = ((int64_t)(zl + B2R_PAD_LO) * R + x) * R + y;
-    const int64_t out = ((int64_t)x * R + y) * nz + zl;
+    const int z = (int)((t / R) % R);
+    const int xl = (int)(t / ((int64_t)R * R));                     // x plane of the slab (nz = planes owned)
+    const int64_t in = ((int64_t)(xl + B2R_PAD_LO) * R + z) * R + y;
+    const int64_t out = ((int64_t)xl * R + y) * R + z;              // Open3D's [x][y][z], x restricted to the slab
     const float2 q = tsdfw[in];
     if (out_tsdf) out_tsdf[out] = q.x;
     if (out_w) out_w[out] = q.y;
@@ -38,10 +38,10 @@ __global__ void volume_import_kernel(float2* __restrict__ tsdfw, uint32_t* __res
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     const int y = (int)(t % R);
-    const int x = (int)((t / R) % R);
-    const int zl = (int)(t / ((int64_t)R * R));
-    const int64_t dst = ((int64_t)(zl + B2R_PAD_LO) * R + x) * R + y;
-    const int64_t src = ((int64_t)x * R + y) * nz + zl;
+    const int z = (int)((t / R) % R);
+    const int xl = (int)(t / ((int64_t)R * R));
+    const int64_t dst = ((int64_t)(xl + B2R_PAD_LO) * R + z) * R + y;
+    const int64_t src = ((int64_t)xl * R + y) * R + z;
     tsdfw[dst] = make_float2(in_tsdf[src], in_w[src]);
     if (color && color_type != 0 && in_color) {
         if (color_type == 1) {
@@ -69,7 +69,7 @@ int b2r_volume_export(b2r_ctx* ctx, const b2r_volume* vol, float* d_tsdf_out, fl
     B2R_CHECK(ctx && vol && vol->d_tsdfw, -1, "b2r_volume_export: NULL argument");
     B2R_CUDA(cudaSetDevice(ctx->device));
     B2R_CUDA(join_side(ctx, S(stream)));   // items kernels of earlier integrate calls run on the side stream
-    const int nz = vol->z_end - vol->z_begin, R = vol->resolution;
+    const int nz = vol->x_end - vol->x_begin, R = vol->resolution;
     const int64_t n = (int64_t)nz * R * R;
     if (n == 0) return 0;
     volume_export_kernel<<<cdiv(n, 256), 256, 0, S(stream)>>>((const float2*)vol->d_tsdfw,
@@ -85,7 +85,7 @@ int b2r_volume_import(b2r_ctx* ctx, const b2r_volume* vol, const float* d_tsdf_i
     ctx->write_gen++;
     B2R_CUDA(cudaSetDevice(ctx->device));
     B2R_CUDA(join_side(ctx, S(stream)));   // items kernels of earlier integrate calls run on the side stream
-    const int nz = vol->z_end - vol->z_begin, R = vol->resolution;
+    const int nz = vol->x_end - vol->x_begin, R = vol->resolution;
     const int64_t n = (int64_t)nz * R * R;
     if (n == 0) return 0;
     volume_import_kernel<<<cdiv(n, 256), 256, 0, S(stream)>>>((float2*)vol->d_tsdfw, (uint32_t*)vol->d_color, R, nz,

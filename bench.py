@@ -368,7 +368,7 @@ def run_gpu(args):
         for _ in range(3):
             zb, ze = ranges[rank]
             v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
-                                                            syn.volume_origin(L), z_range=(zb, ze), device=local)
+                                                            syn.volume_origin(L), x_range=(zb, ze), device=local)
             v.count_updates = False
             for k in range(3):
                 v.integrate_device(depth_f[k % nf], rgb[k % nf], intr, exts[k % nf])
@@ -399,7 +399,7 @@ def run_gpu(args):
         ranges = parallel.balanced_slab_ranges(work, n_)
         zb, ze = ranges[r_]
     vol = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
-                                                      syn.volume_origin(L), z_range=(zb, ze), device=local)
+                                                      syn.volume_origin(L), x_range=(zb, ze), device=local)
     vol.count_updates = False   # switched on for the counting pass and the e2e pass only
     # pinned host copies for the e2e arm
     d16_h = d16.cpu().pin_memory()

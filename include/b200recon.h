@@ -17,9 +17,11 @@
  *   - transforms are row-major double[16]; `extrinsic` = world->camera as in Open3D.
  *
  * Volume memory layout (device, chosen for coalescing on B200 -- NOT Open3D's AoS):
- *   slab of planes z in [z_begin, z_end) of an R x R x R cube, stored z-slowest, y-fastest with
- *   B2R_PAD_LO halo planes below and B2R_PAD_HI above:
- *       plane p = z - z_begin + B2R_PAD_LO,   index = (p * R + x) * R + y
+ *   slab of planes x in [x_begin, x_end) of an R x R x R cube, stored x-slowest, y-fastest (Open3D's own index is
+ *   x*R*R + y*R + z: x-slowest too) with B2R_PAD_LO halo planes below and B2R_PAD_HI above:
+ *       plane p = x - x_begin + B2R_PAD_LO,   index = (p * R + z) * R + y
+ *   A slab owns WHOLE (x, y) columns: Open3D's float32 z-chain of a column and the per-column planning of a frame run
+ *   once per column whatever the number of slabs, and the z steps of a column are R*8 bytes apart.
  *   tsdfw : float2 {tsdf, weight} per voxel (8 B);
  *   color : uint32 packed 10:10:10 fixed point (value*4, R in bits 0-9, G 10-19, B 20-29).
  */
@@ -47,14 +49,14 @@ typedef struct b2r_intrinsic {
  * color_type: 0 NoColor, 1 RGB8, 2 Gray32 (TSDFVolumeColorType). */
 typedef struct b2r_volume {
     int32_t resolution;        /* R */
-    int32_t z_begin, z_end;    /* planes owned by this slab (whole cube: 0, R) */
+    int32_t x_begin, x_end;    /* planes owned by this slab (whole cube: 0, R) */
     int32_t color_type;
     double voxel_length;       /* length / resolution */
     double sdf_trunc;
     double origin[3];
-    void* d_tsdfw;             /* float2 [(z_end-z_begin+PAD_LO+PAD_HI) * R * R] */
+    void* d_tsdfw;             /* float2 [(x_end-x_begin+PAD_LO+PAD_HI) * R * R] */
     void* d_color;             /* uint32, same count; NULL when color_type == 0 */
-    void* d_rows;              /* optional uint8 [(z_end-z_begin+PAD_LO+PAD_HI) * R]: 1 = row (plane, x) may hold a voxel
+    void* d_rows;              /* optional uint8 [(x_end-x_begin+PAD_LO+PAD_HI) * R]: 1 = row (plane x, z) may hold a voxel
                                 * with weight != 0.  Maintained by the library (integrate marks, reset clears, import
                                 * sets all); halo planes travel with the volume's halo planes.  Extraction classifies
                                 * only cube rows next to a marked row; NULL = no information, every row is read. */
@@ -168,7 +170,7 @@ int b2r_volume_import(b2r_ctx* ctx, const b2r_volume* vol, const float* d_tsdf_i
                       const float* d_color_in, void* stream);
 
 /* ---- marching cubes (O3D UniformTSDFVolume.extract_triangle_mesh()) ---------------------- */
-/* Pass 1 (blocking): classify + count + scan.  Halo planes [z_begin-1, z_end] must be valid when the
+/* Pass 1 (blocking): classify + count + scan.  Halo planes [x_begin-1, x_end] must be valid when the
  * slab is not the whole cube.  Returns this slab's vertex and triangle counts. */
 int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_vertices, int64_t* n_triangles,
                            void* stream);

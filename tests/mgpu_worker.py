@@ -59,15 +59,15 @@ def main():
     work = parallel.probe_plane_work(L, R, trunc, origin, probe, intr, probe_resolution=32)
     ranges = parallel.balanced_slab_ranges(work, world)
     assert ranges[0][0] == 0 and ranges[-1][1] == R
-    vol = parallel.SlabVolume(L, R, trunc, RGB8, origin, z_ranges=ranges)
+    vol = parallel.SlabVolume(L, R, trunc, RGB8, origin, x_ranges=ranges)
     ref = orc.UniformTSDFVolume(L, R, trunc, 1, origin)
     for d16, rgb, ext in frames:
         vol.integrate_host(d16, rgb, intr, ext)
         ref.integrate(orc.depth_to_float(d16), rgb, hp.kt(K), ext)
     ts, w, _ = vol.local.export_arrays()
-    zb, ze = vol.z_begin, vol.z_end
-    assert np.array_equal(w, ref.weight()[:, :, zb:ze]), "slab weights differ"
-    assert np.array_equal(ts.view(np.uint32), ref.tsdf()[:, :, zb:ze].view(np.uint32)), "slab tsdf differs"
+    zb, ze = vol.x_begin, vol.x_end
+    assert np.array_equal(w, ref.weight()[zb:ze]), "slab weights differ"
+    assert np.array_equal(ts.view(np.uint32), ref.tsdf()[zb:ze].view(np.uint32)), "slab tsdf differs"
     mesh = vol.extract_triangle_mesh()
     pcd = vol.extract_point_cloud()
     if rank == 0:
@@ -89,8 +89,8 @@ def main():
     wn = (rng.random((R2, R2, R2)) > 0.08).astype(np.float32) * rng.integers(1, 5, (R2, R2, R2)).astype(np.float32)
     coln = (np.round(rng.uniform(0, 255, (R2, R2, R2, 3)) * 4) / 4).astype(np.float32)
     vol2 = parallel.SlabVolume(1.2, R2, 0.1, RGB8, (0.1, -0.2, 0.3))
-    zb, ze = vol2.z_begin, vol2.z_end
-    vol2.local.import_arrays(tsn[:, :, zb:ze], wn[:, :, zb:ze], coln[:, :, zb:ze])
+    zb, ze = vol2.x_begin, vol2.x_end
+    vol2.local.import_arrays(tsn[zb:ze], wn[zb:ze], coln[zb:ze])
     mesh2 = vol2.extract_triangle_mesh()
     pcd2 = vol2.extract_point_cloud()
     if rank == 0:

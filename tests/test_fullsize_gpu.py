@@ -29,9 +29,9 @@ def _frames(n):
     return out
 
 
-def _volume(o3d, z_range=None):
+def _volume(o3d, x_range=None):
     v = o3d.pipelines.integration.UniformTSDFVolume(L, R, TRUNC, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
-                                                    syn.volume_origin(L), z_range=z_range)
+                                                    syn.volume_origin(L), x_range=x_range)
     v.count_updates = True
     return v
 
@@ -46,7 +46,7 @@ def test_full_size_volume(o3d, orc):
     whole._ctx.sync()
     n_whole = whole.updates()
     assert n_whole > 100e6
-    PL = 1   # B2R_PAD_LO: padded plane p holds z = z_begin - 1 + p
+    PL = 1   # B2R_PAD_LO: padded plane p holds x = x_begin - 1 + p; memory is [x plane][z][y]
 
     # ---- oracle parity on three x-ranges (left part of the frustum, centre, right part)
     for x0 in (300, 508, 700):
@@ -54,7 +54,7 @@ def test_full_size_volume(o3d, orc):
         n_ref = 0
         for d16, rgb, ext in frames:
             n_ref += ref.integrate(orc.depth_to_float(d16), rgb, hp.KT640, ext)
-        g = whole._tsdfw[PL:PL + R, x0:x0 + 8].permute(1, 2, 0, 3).contiguous().cpu().numpy()   # [x, y, z, {tsdf, w}]
+        g = whole._tsdfw[PL + x0:PL + x0 + 8].permute(0, 2, 1, 3).contiguous().cpu().numpy()   # [x, y, z, {tsdf, w}]
         assert np.array_equal(g[..., 1], ref.weight()), "weights must be bit-exact (x-range %d)" % x0
         assert np.array_equal(g[..., 0].view(np.uint32), ref.tsdf().view(np.uint32)), "tsdf must be bit-exact"
         assert int((g[..., 1] > 0).sum()) > 0 and n_ref > 0
@@ -63,7 +63,7 @@ def test_full_size_volume(o3d, orc):
 
     # ---- slab consistency
     n_slabs = 0
-    for zr in ((0, 117), (117, 171), (171, 1024)):
+    for zr in ((0, 417), (417, 471), (471, 1024)):
         s = _volume(o3d, zr)
         for d16, rgb, ext in frames:
             s.integrate_host(d16, rgb, intr, ext)

@@ -10,14 +10,14 @@ from b200recon import synthetic as syn
 pytestmark = pytest.mark.gpu
 
 
-def _run_pair(o3d, orc, R, L, trunc, frames, K, color_type=1, z_ranges=None, origin=None, via_host=False):
+def _run_pair(o3d, orc, R, L, trunc, frames, K, color_type=1, x_ranges=None, origin=None, via_host=False):
     origin = syn.volume_origin(L) if origin is None else origin
     kt = hp.kt(K)
     ref = orc.UniformTSDFVolume(L, R, trunc, color_type, origin)
     intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], *kt)
     ct = o3d.pipelines.integration.TSDFVolumeColorType(color_type)
-    z_ranges = z_ranges or [(0, R)]
-    vols = [o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, ct, origin, z_range=zr) for zr in z_ranges]
+    x_ranges = x_ranges or [(0, R)]
+    vols = [o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, ct, origin, x_range=zr) for zr in x_ranges]
     for v in vols:
         v.count_updates = True
     n_ref = 0
@@ -45,17 +45,17 @@ def _compare(ref, vols, n_ref, color_type, color_tol=1.5):
     n_gpu = 0
     for v in vols:
         ts, w, col = v.export_arrays()
-        zb, ze = v.z_begin, v.z_end
-        assert np.array_equal(w, w_ref[:, :, zb:ze]), "weights must be bit-exact"
-        assert np.array_equal(ts.view(np.uint32), t_ref[:, :, zb:ze].view(np.uint32)), "tsdf must be bit-exact"
-        assert np.abs(ts - t_ref[:, :, zb:ze]).max() <= 1e-5
+        zb, ze = v.x_begin, v.x_end
+        assert np.array_equal(w, w_ref[zb:ze]), "weights must be bit-exact"
+        assert np.array_equal(ts.view(np.uint32), t_ref[zb:ze].view(np.uint32)), "tsdf must be bit-exact"
+        assert np.abs(ts - t_ref[zb:ze]).max() <= 1e-5
         if color_type == 1:
             m = w > 0
-            err = np.abs(col - c_ref[:, :, zb:ze])[m]
+            err = np.abs(col - c_ref[zb:ze])[m]
             assert err.size == 0 or err.max() <= color_tol, err.max()  # packed 10:10:10 mean vs float64
         elif color_type == 2:
             m = w > 0
-            assert not m.any() or np.abs(col[..., 0] - c_ref[:, :, zb:ze, 0])[m].max() <= 1e-5
+            assert not m.any() or np.abs(col[..., 0] - c_ref[zb:ze, :, :, 0])[m].max() <= 1e-5
         n_gpu += v.updates()
     assert n_gpu == n_ref
     assert n_ref > 0
@@ -96,9 +96,9 @@ def test_integrate_z_slabs_match_whole(o3d, orc):
     slabs is bit-identical to the single volume."""
     K = hp.small_intrinsic(320, 240)
     frames = hp.make_frames(4, K)
-    ref, vols, n = _run_pair(o3d, orc, 96, 0.384, 0.016, frames, K, z_ranges=[(0, 24), (24, 48), (48, 72), (72, 96)])
+    ref, vols, n = _run_pair(o3d, orc, 96, 0.384, 0.016, frames, K, x_ranges=[(0, 24), (24, 48), (48, 72), (72, 96)])
     _compare(ref, vols, n, 1)
-    ref, vols, n = _run_pair(o3d, orc, 96, 0.384, 0.016, frames, K, z_ranges=[(0, 37), (37, 96)])
+    ref, vols, n = _run_pair(o3d, orc, 96, 0.384, 0.016, frames, K, x_ranges=[(0, 37), (37, 96)])
     _compare(ref, vols, n, 1)
 
 

@@ -228,6 +228,6 @@ def test_mesh_checksum_is_order_and_numbering_independent():
 
 def test_local_slabs_rejects_bad_partitions():
     with pytest.raises(RuntimeError):
-        parallel.LocalSlabs(1.0, 32, 0.1, z_ranges=[(0, 10), (12, 32)])
+        parallel.LocalSlabs(1.0, 32, 0.1, x_ranges=[(0, 10), (12, 32)])
     with pytest.raises(RuntimeError):
-        parallel.LocalSlabs(1.0, 32, 0.1, z_ranges=[(0, 1), (1, 32)])          # thinner than the halo
+        parallel.LocalSlabs(1.0, 32, 0.1, x_ranges=[(0, 1), (1, 32)])          # thinner than the halo

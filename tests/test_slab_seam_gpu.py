@@ -1,4 +1,4 @@
-"""The z-slab seam logic of SURVEY.md 8(e) on ONE GPU: `parallel.LocalSlabs` cuts a cube into unequal slabs that live in
+"""The slab seam logic of SURVEY.md 8(e) on ONE GPU: `parallel.LocalSlabs` cuts a cube into unequal slabs (x planes) that live in
 one process, fills their halo planes with device copies (the planes `parallel.halo_plan` moves over NCCL between
 ranks), runs b2r_extract_mesh_count / _vertices (vertex_base) / b2r_mesh_seam_buffers / _triangles per slab and
 concatenates.  The union must be the oracle's single-volume mesh / point cloud -- the check tests/mgpu_worker.py does
@@ -37,30 +37,30 @@ def _check_points(ref_pc, pcd, vl):
     assert np.abs(N[oa] - Ng[ob]).max() < 1e-9
 
 
-@pytest.mark.parametrize("ranges", [[(0, 10), (10, 14), (14, 96)], [(0, 10), (10, 12), (12, 15), (15, 96)]])
+@pytest.mark.parametrize("ranges", [[(0, 40), (40, 44), (44, 96)], [(0, 46), (46, 48), (48, 51), (51, 96)]])
 def test_three_unequal_slabs_frames_scene(o3d, orc, ranges):
     """Fused frames: every slab bit-exact against the oracle's planes, union mesh / points == single-volume oracle.
-    The thin middle slabs (4 and 2-3 planes) sit where the table (z index 9.6) and the object (up to ~19.6) are, so the
-    seams cut the surface."""
+    Slabs are ranges of x planes; the thin middle slabs (4 and 2-3 planes) sit where the object is (x index ~27-69),
+    so the seams cut the table and the object."""
     R, L, trunc = 96, 0.384, 0.016
     K = hp.small_intrinsic(320, 240)
     frames = hp.make_frames(5, K)
     origin = syn.volume_origin(L)
     RGB8 = o3d.pipelines.integration.TSDFVolumeColorType.RGB8
     intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], *hp.kt(K))
-    vol = parallel.LocalSlabs(L, R, trunc, RGB8, origin, z_ranges=ranges)
+    vol = parallel.LocalSlabs(L, R, trunc, RGB8, origin, x_ranges=ranges)
     ref = orc.UniformTSDFVolume(L, R, trunc, 1, origin)
     for d16, rgb, ext in frames:
         vol.integrate_host(d16, rgb, intr, ext)
         ref.integrate(orc.depth_to_float(d16), rgb, hp.kt(K), ext)
     for v, (zb, ze) in zip(vol.slabs, ranges):
         ts, w, _ = v.export_arrays()
-        assert np.array_equal(w, ref.weight()[:, :, zb:ze]), "slab weights differ"
-        assert np.array_equal(ts.view(np.uint32), ref.tsdf()[:, :, zb:ze].view(np.uint32)), "slab tsdf differs"
+        assert np.array_equal(w, ref.weight()[zb:ze]), "slab weights differ"
+        assert np.array_equal(ts.view(np.uint32), ref.tsdf()[zb:ze].view(np.uint32)), "slab tsdf differs"
     ref_mesh = ref.extract_triangle_mesh()
     assert len(ref_mesh[0]) > 1000
     # the surface must really cross the seams: vertices on both sides of every cut
-    zv = (ref_mesh[0][:, 2] - origin[2]) / (L / R)
+    zv = (ref_mesh[0][:, 0] - origin[0]) / (L / R)        # slab axis: x
     for (_, cut) in ranges[:-1]:
         assert (zv < cut).any() and (zv > cut).any()
     _check_mesh(ref_mesh, vol.extract_triangle_mesh(), L / R, 2.0 / 255.0)
@@ -75,7 +75,7 @@ def test_white_noise_volume_across_seams(o3d, orc):
     w = (rng.random((R, R, R)) > 0.08).astype(np.float32) * rng.integers(1, 5, (R, R, R)).astype(np.float32)
     col = (np.round(rng.uniform(0, 255, (R, R, R, 3)) * 4) / 4).astype(np.float32)
     RGB8 = o3d.pipelines.integration.TSDFVolumeColorType.RGB8
-    vol = parallel.LocalSlabs(1.2, R, 0.1, RGB8, (0.1, -0.2, 0.3), z_ranges=[(0, 9), (9, 11), (11, 20), (20, 27)])
+    vol = parallel.LocalSlabs(1.2, R, 0.1, RGB8, (0.1, -0.2, 0.3), x_ranges=[(0, 9), (9, 11), (11, 20), (20, 27)])
     vol.import_arrays(ts, w, col)
     ref = orc.UniformTSDFVolume(1.2, R, 0.1, 1, (0.1, -0.2, 0.3))
     ref.tsdf()[:] = ts

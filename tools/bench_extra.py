@@ -112,7 +112,7 @@ def sharded_mesh_bench(vol, ranges, voxel_length):
     import torch.distributed as dist
     from b200recon import parallel
     rank, world = parallel.world_info()
-    sv = parallel.SlabVolume(vol.length, vol.resolution, vol.sdf_trunc, vol.color_type, vol.origin, z_ranges=ranges,
+    sv = parallel.SlabVolume(vol.length, vol.resolution, vol.sdf_trunc, vol.color_type, vol.origin, x_ranges=ranges,
                              local=vol)
     sv.extract_triangle_mesh()                       # warm-up: scratch allocation, NCCL channel set-up
     sv._halo_valid = False
@@ -190,7 +190,7 @@ def tsdf2048_bench(rank, world, device, steps=64, n_frames=32):
         return e0.elapsed_time(e1) / n
 
     for _ in range(2 if world > 1 else 0):
-        v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, RGB8, origin, z_range=ranges[rank], device=device)
+        v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, RGB8, origin, x_range=ranges[rank], device=device)
         tt = torch.zeros(world, dtype=torch.float64, device=dev)
         tt[rank] = per_frame_ms(v, len(frames))
         dist.all_reduce(tt)
@@ -198,7 +198,7 @@ def tsdf2048_bench(rank, world, device, steps=64, n_frames=32):
         del v
         torch.cuda.empty_cache()
     parallel.check_same_ranges(ranges, R, device=dev)
-    v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, RGB8, origin, z_range=ranges[rank], device=device)
+    v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, RGB8, origin, x_range=ranges[rank], device=device)
     ms = per_frame_ms(v, steps)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:

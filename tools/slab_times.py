@@ -24,7 +24,7 @@ from b200recon import parallel, _lib
 
 def slab_time(a, b):
     v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
-                                                    syn.volume_origin(L), z_range=(a, b))
+                                                    syn.volume_origin(L), x_range=(a, b))
     for f in frames[:3]:
         v.integrate_host(f[0], f[1], intr, f[2])
     ctx.kernel_timing(True)
@@ -56,7 +56,7 @@ if auto:      # emulate bench.py's setup for N ranks on one GPU: probe -> cost p
 
 for a, b in zip(cuts[:-1], cuts[1:]):
     v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
-                                                    syn.volume_origin(L), z_range=(a, b))
+                                                    syn.volume_origin(L), x_range=(a, b))
     v.count_updates = True
     for f in frames[:3]:
         v.integrate_host(f[0], f[1], intr, f[2])

@@ -41,7 +41,7 @@ def run(v):
 print("workload %s, %d frames, %s frames; times in us (median [p10 p90])" % (wl, len(frames), mode))
 for a, b in zip(cuts[:-1], cuts[1:]):
     v = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
-                                                    syn.volume_origin(L), z_range=(a, b))
+                                                    syn.volume_origin(L), x_range=(a, b))
     run(v)
     ctx.sync()
     ctx.trace(len(frames))
