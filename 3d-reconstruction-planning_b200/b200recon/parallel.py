@@ -47,7 +47,7 @@ def slab_ranges(resolution, world):
 
 
 def balanced_slab_ranges(plane_work, world, min_planes=4):
-    """Contiguous z-slabs with (nearly) equal WORK instead of equal plane counts.  Integration only touches the
+    """Contiguous slabs (x planes) with (nearly) equal WORK instead of equal plane counts.  Integration only touches the
     voxels between the cameras and the surfaces, which on a table-top orbit is the lower part of the cube: equal
     slabs leave most ranks idle.  `plane_work[z]` = expected voxel updates per frame sequence in plane z (see
     `probe_plane_work`); returns [(x_begin, x_end)] per rank, every slab at least `min_planes` thick (halo)."""
@@ -273,7 +273,7 @@ class _RawCuda:
 
 
 class SlabVolume:
-    """`UniformTSDFVolume` sharded into z-slabs over the ranks of a process group (BASELINE configs 3 and 5).
+    """`UniformTSDFVolume` sharded into slabs of x planes over the ranks of a process group (BASELINE configs 3 and 5).
 
         vol = SlabVolume(length, resolution, sdf_trunc, color_type, origin)   # every rank, same arguments
         vol.integrate(rgbd, intrinsic, extrinsic)                             # every rank, every frame
@@ -439,7 +439,7 @@ def _raw_i32(ptr, n, tdev):
 
 
 class LocalSlabs:
-    """The z-slab decomposition of `SlabVolume` without a process group: every slab is a `UniformTSDFVolume` with its
+    """The slab decomposition of `SlabVolume` without a process group: every slab is a `UniformTSDFVolume` with its
     own library context (own scratch, side stream and extraction state) on one device of this process, and the
     exchange steps -- halo planes, the seam plane of the vertex-id table -- are device-to-device copies instead of
     NCCL messages.  Same kernels, same C-ABI calls (`vertex_base`, `b2r_mesh_seam_buffers`), same result: the

@@ -5,7 +5,7 @@ A.3/A.4, rows a5/a6/f4).
     vol.integrate(rgbd, intrinsic, extrinsic)
     mesh = vol.extract_triangle_mesh();  pcd = vol.extract_point_cloud()
 
-Multi-GPU: pass `x_range=(x_begin, x_end)` to own one z-slab of the cube; `parallel.SlabVolume` wires
+Multi-GPU: pass `x_range=(x_begin, x_end)` to own one slab (a range of x planes) of the cube; `parallel.SlabVolume` wires
 the slabs of all ranks together (halo exchange + gather over NCCL).
 """
 import ctypes as C
@@ -333,7 +333,7 @@ class ScalableTSDFVolume(UniformTSDFVolume):
 
     B200 design: the units are NOT hashed.  They live at their place in a dense backing cube in HBM (a unit that was
     never opened holds weight 0, which every extraction rule of Open3D treats exactly like a missing unit), so mesh /
-    point extraction, persistence and the z-slab machinery are the dense kernels unchanged, and "scalable" is the
+    point extraction, persistence and the slab machinery are the dense kernels unchanged, and "scalable" is the
     per-frame list of touched units (`b2r_integrate_units`).  Open3D's volume is unbounded; this one covers
     `resolution`^3 voxels (multiple of the unit size) whose first unit is `unit_offset` (default: cube centred on the
     world origin; `origin=` snaps down to a unit boundary).  Unit touches outside the cube are counted

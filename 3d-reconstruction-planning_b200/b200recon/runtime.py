@@ -92,7 +92,7 @@ def ctx(device=None):
 
 def new_context(device=None):
     """A further library context on `device` (own scratch, own side/copy streams, own extraction state): one per
-    z-slab when several slabs of a cube live in ONE process (parallel.LocalSlabs)."""
+    slab when several slabs of a cube live in ONE process (parallel.LocalSlabs)."""
     return Context(default_device() if device is None else int(device))
 
 

@@ -7,7 +7,7 @@
 A "step" is the integration of ONE synthetic 640x480 RGB-D frame of the orbit into the dense TSDF+colour
 volume.  Default workload `tsdf1024` = BASELINE config[2] (1024^3 @ 2 mm, 256-frame orbit; the size the
 north_star target is quoted on, and it fits one B200: 12.9 GB); `tsdf512` = config[1] (512^3, 64 frames).
-For N > 1 (torchrun, one rank per GPU) the cube is z-slab sharded: every rank integrates every frame
+For N > 1 (torchrun, one rank per GPU) the cube is sharded into slabs of x planes (x-slabs: whole columns per rank): every rank integrates every frame
 into its own slab, no data-path collective -> total work fixed -> "scaling": "strong".
 
   value     frames/s with the frames already resident in HBM (ray-cast on the GPU before timing).
@@ -345,7 +345,7 @@ def run_gpu(args):
     for i in range(nf):
         _lib.check(_lib.load().b2r_depth_to_float(ctx.handle, runtime.ptr(d16[i]), 1, K["height"], K["width"], 1000.0,
                                                   3.0, runtime.ptr(depth_f[i]), ctx.stream()))
-    # z-slab owned by this rank.  Equal plane counts would leave most ranks idle (a table-top orbit only touches the
+    # slab (x planes) owned by this rank.  Equal plane counts would leave most ranks idle (a table-top orbit only touches the
     # planes between the cameras and the table), so the slab boundaries come from a coarse probe integration of 16
     # frames of the sequence: contiguous slabs of equal WORK (parallel.balanced_slab_ranges); every rank computes the
     # same boundaries, no collective.
@@ -560,7 +560,7 @@ def run_gpu(args):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "rank_ms_per_step": rank_ms_per_step,
             "config": {"workload": args.workload, "resolution": R, "voxel_mm": 1000.0 * L / R, "frames_in_orbit": len(poses),
-                       "frame": "%dx%d uint16 depth + uint8 rgb" % (K["width"], K["height"]), "sharding": "z-slab x%d" % world, "slab_boundaries": [a for a, _ in ranges] + [R],
+                       "frame": "%dx%d uint16 depth + uint8 rgb" % (K["width"], K["height"]), "sharding": "x-slab x%d (slabs of x planes, whole columns per rank)" % world, "slab_boundaries": [a for a, _ in ranges] + [R],
                        "l2": "volume (%.1f GB) >> L2; consecutive frames touch overlapping voxels as in a real "
                              "sequence, no artificial flush" % (R ** 3 * 12 / 1e9)},
             "voxel_updates_per_s": upd / (ms * 1e-3),

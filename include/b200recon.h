@@ -154,8 +154,9 @@ int b2r_integrate_units(b2r_ctx* ctx, const b2r_volume* vol, const float* d_dept
  * refined reciprocal; this runs n pseudo-random cases (projection-like, full-range, running-mean-like and
  * near-half-way quotients) through that code and through the `/` operator; mismatches[4] = count per family. */
 int b2r_selftest_div(b2r_ctx* ctx, int64_t n, uint32_t seed, int64_t* mismatches, void* stream);
-/* Device self-test (blocking): planning starts a z-slab's float32 chains `pt_camera += col(2)` at the slab
- * without walking the planes below it (mantissa arithmetic inside a binade, real steps across binade edges / ties);
+/* Device self-test (blocking): chain_jump (csrc/tsdf_integrate.cu, compiled out by default) advances Open3D's float32
+ * chains `pt_camera += col(2)` n steps without walking them (mantissa arithmetic inside a binade, real steps
+ * across binade edges / ties);
  * this runs n pseudo-random and adversarial (start, increment, steps) cases through that code and through the
  * stepped chain; *mismatches = cases whose bits differ. */
 int b2r_selftest_chain(b2r_ctx* ctx, int64_t n, uint32_t seed, int64_t* mismatches, void* stream);

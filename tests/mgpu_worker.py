@@ -1,6 +1,6 @@
 """Multi-GPU parity worker, launched by tests/test_multi_gpu.py (or by hand) as
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/mgpu_worker.py
-One rank per GPU over NCCL.  z-slab SlabVolume vs the CPU oracle's single volume: every slab bit-exact,
+One rank per GPU over NCCL.  SlabVolume (slabs of x planes) vs the CPU oracle's single volume: every slab bit-exact,
 the gathered mesh / point cloud identical to the oracle's, white-noise volume (all cube cases across the
 seams), round-robin batched ICP identical to the single-rank batch."""
 import os

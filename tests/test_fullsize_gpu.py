@@ -3,7 +3,7 @@ checks that do not need the whole cube on the CPU:
 
   * bit-exact parity with the ORACLE on x-ranges of the cube (Open3D parallelises Integrate over x, an x-range is
     a complete sub-problem: 8 x 1024 x 1024 voxels finish in seconds on the host);
-  * slab consistency: three unequal z-slabs integrated separately are bit-identical, plane for plane, to the single
+  * slab consistency: three unequal slabs (x planes) integrated separately are bit-identical, plane for plane, to the single
     volume, and their update counts add up (chain replay across slabs, SURVEY.md 8(e));
   * the mesh of the full volume is welded and consistently oriented: every directed edge occurs exactly once, every
     index is in range, counts are stable across two extractions; surface points == sign-change edges of the same

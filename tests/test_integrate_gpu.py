@@ -91,8 +91,8 @@ def test_integrate_color_types(o3d, orc, color_type):
     _compare(ref, vols, n, color_type)
 
 
-def test_integrate_z_slabs_match_whole(o3d, orc):
-    """z-slab sharding: every slab replays the float32 chain from z=0, so the union of the
+def test_integrate_slabs_match_whole(o3d, orc):
+    """slab sharding: slabs are ranges of x planes and own whole columns, so the union of the
     slabs is bit-identical to the single volume."""
     K = hp.small_intrinsic(320, 240)
     frames = hp.make_frames(4, K)

@@ -103,7 +103,7 @@ def mesh_bench(vol, reps=2):
 
 
 def sharded_mesh_bench(vol, ranges, voxel_length):
-    """extract_triangle_mesh of the z-slab sharded cube through parallel.SlabVolume (every rank calls this with its own
+    """extract_triangle_mesh of the slab-sharded cube through parallel.SlabVolume (every rank calls this with its own
     slab `vol` = slab `ranges[rank]`): halo exchange of {tsdf,w}/colour planes -> per-slab marching cubes with global
     vertex ids -> seam plane of the id table -> gather on rank 0.  CUDA-event time per phase (max over ranks), the
     gathered counts and an order-independent digest of the mesh (parallel.mesh_checksum at 1e-4 voxel): the digest
@@ -146,7 +146,7 @@ def sharded_mesh_bench(vol, ranges, voxel_length):
 
 def tsdf2048_bench(rank, world, device, steps=64, n_frames=32):
     """BASELINE configs[4] in the driver's own record (the driver only runs the default workload): 1280x720 frames into a
-    2048^3 TSDF+colour cube (4.096 m @ 2 mm, 103 GB) z-slab sharded over the `world` ranks of this run.  Slab boundaries:
+    2048^3 TSDF+colour cube (4.096 m @ 2 mm, 103 GB) sharded into x-slabs over the `world` ranks of this run.  Slab boundaries:
     the coarse work probe + two feedback steps on per-frame time, like the main workload.  Frames resident in HBM,
     CUDA-event time of `steps` integrate calls, max over ranks; every rank must call it."""
     import torch
@@ -206,7 +206,7 @@ def tsdf2048_bench(rank, world, device, steps=64, n_frames=32):
     ms = float(t.item())
     del v
     torch.cuda.empty_cache()
-    return {"workload": "tsdf2048: 1280x720 frames into a 2048^3 TSDF+colour cube (4.096 m @ 2 mm, 103 GB), z-slab x%d" % world,
+    return {"workload": "tsdf2048: 1280x720 frames into a 2048^3 TSDF+colour cube (4.096 m @ 2 mm, 103 GB), x-slab x%d" % world,
             "frames_per_s": 1000.0 / ms, "ms_per_step": ms, "steps": steps, "slab_boundaries": [a for a, _ in ranges] + [R],
             "frames": "%d resident frames of the 1000-frame orbit, cycled" % len(frames)}
 

@@ -1,5 +1,5 @@
 """Device-side timeline of consecutive integrate calls on ONE GPU (b2r_ctx_trace: the kernels stamp %globaltimer
-themselves), for the whole cube or for the z-slabs of an N-way split:
+themselves), for the whole cube or for the slabs (x planes) of an N-way split:
     python tools/timeline_probe.py 0,1024                 # the whole cube
     python tools/timeline_probe.py 0,109,131,153,176,199,224,259,1024 [tsdf1024] [host|device]
 Prints, per slab, the median duration of frame_prepare / integrate_plan / integrate_items, the step (start of one
