@@ -59,7 +59,7 @@ struct Scratch {
 // Everything one frame needs between its preparation and its items kernel.  Two slots alternate so that
 // frame i+1 is prepared and planned on the caller's stream while frame i still streams on the side stream.
 #ifndef B2R_FRAME_SLOTS
-#define B2R_FRAME_SLOTS 2   // 3 measured no gain: the plan kernel needs free registers beside the persistent kernel, not more slack
+#define B2R_FRAME_SLOTS 3   // slots allocated; how many are cycled through is decided per call (integrate_prepared)
 #endif
 struct b2r_frame_slot {
     b2r::Scratch dm, rgba, mip;      // prepared frame: {depth, multiplier} pairs, colour words, max-depth pyramid

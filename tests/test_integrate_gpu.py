@@ -120,6 +120,22 @@ def test_integrate_many_frames_color_drift(o3d, orc):
     _compare(ref, vols, n, 1, color_tol=3.0)
 
 
+def test_integrate_256_frames_color_bound(o3d, orc, capsys):
+    """The packed 10:10:10 running mean rounds to a quarter level at every update (and stops moving once
+    |x - c| * 4 / (w + 1) < 1/2), Open3D keeps a float64 mean: the deviation after a 256-frame orbit -- the length of the
+    bench sequence -- is bounded here.  TSDF and weights stay bit-exact over the same 256 frames."""
+    K = hp.small_intrinsic(160, 120)
+    frames = hp.make_frames(256, K)
+    ref, vols, n = _run_pair(o3d, orc, 64, 0.384, 0.024, frames, K, via_host=True)
+    _compare(ref, vols, n, 1, color_tol=6.0)
+    _, w, col = vols[0].export_arrays()
+    err = np.abs(col - ref.color())[w > 0]
+    with capsys.disabled():
+        print("\n[color drift] 256 frames: max |dc| = %.3f / 255, mean %.4f, p99.9 %.3f, max weight %d"
+              % (err.max(), err.mean(), np.percentile(err, 99.9), int(w.max())))
+    assert err.mean() < 0.5
+
+
 def test_integrate_errors(o3d):
     intr = o3d.camera.PinholeCameraIntrinsic(160, 120, 150.0, 150.0, 80.0, 60.0)
     vol = o3d.pipelines.integration.UniformTSDFVolume(0.4, 32, 0.02, o3d.pipelines.integration.TSDFVolumeColorType.RGB8)
