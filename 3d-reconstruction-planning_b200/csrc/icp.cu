@@ -100,6 +100,9 @@ __global__ void __launch_bounds__(256) icp_bbox_kernel(const double* __restrict_
 }
 
 // Host side of the grid setup: cell size from the radius and the point density, dimensions from the bounding box.
+#ifndef B2R_ICP_WARM
+#define B2R_ICP_WARM 1
+#endif
 #ifndef B2R_ICP_CELL_SPACINGS
 #define B2R_ICP_CELL_SPACINGS 2.5
 #endif
@@ -457,6 +460,14 @@ __global__ void __launch_bounds__(ICP_THREADS, 4) icp_search_kernel(const __grid
     const float feps = P.feps;
     IcpBest B{A.r2, icp_thr(A.r2, feps), -1, 0x7fffffff};
     const float qf0 = (float)(q0 - P.gmin[0]), qf1 = (float)(q1 - P.gmin[1]), qf2 = (float)(q2 - P.gmin[2]);
+    // Warm start: after the first update the pose moves little, so the previous iteration's correspondence is (almost
+    // always) still the nearest neighbour or close to it -- its distance bounds the search from the start, and every row /
+    // cell / ring farther than that is dropped before anything is loaded.  The search stays exact: whatever is closer, or as
+    // close with a lower index, still replaces it.
+    if (B2R_ICP_WARM && St.iter > 0) {
+        const int prev = A.hit[P.src_off + i];
+        if (prev >= 0) icp_exact(A, (uint32_t)prev, q0, q1, q2, feps, B);
+    }
     // reject queries farther than r from the target's bounding box
     double bd = 0.0;
     {
