@@ -84,7 +84,7 @@ int b2r_ctx_destroy(b2r_ctx* c) {
     b2r::Scratch* all[] = {&c->frame_raw_depth, &c->frame_raw_color, &c->frame_f32,
                            &c->small, &c->scan_a, &c->scan_b, &c->mc_code, &c->mc_flags, &c->mc_block_counts,
                            &c->mc_vert_id, &c->pc_block_counts, &c->icp_a, &c->icp_b, &c->icp_c, &c->icp_d,
-                           &c->icp_e, &c->icp_f, &c->cl_a, &c->cl_b, &c->cl_c, &c->cl_d, &c->mc_live, &c->trace};
+                           &c->icp_e, &c->icp_f, &c->cl_a, &c->cl_b, &c->cl_c, &c->cl_d, &c->mc_live, &c->mc_cells, &c->trace};
     for (auto* s : all) s->release();
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     if (c->pinned) cudaFreeHost(c->pinned);

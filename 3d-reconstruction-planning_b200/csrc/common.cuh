@@ -96,7 +96,7 @@ struct b2r_ctx {
     b2r::Scratch small;       // counters, per-frame scalars (zero-initialised on creation)
     b2r::Scratch scan_a, scan_b;
     // marching cubes
-    b2r::Scratch mc_code, mc_flags, mc_block_counts, mc_vert_id, mc_live;
+    b2r::Scratch mc_code, mc_flags, mc_block_counts, mc_vert_id, mc_live, mc_cells;
     int64_t mc_nv = 0, mc_nt = 0;
     int mc_R = 0, mc_zb = 0, mc_ze = 0;
     // Extraction is count -> emit against state kept here: the emit calls check that they see the SAME volume buffer

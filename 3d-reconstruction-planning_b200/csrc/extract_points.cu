@@ -99,33 +99,83 @@ __global__ void __launch_bounds__(PC_THREADS) pc_count2_kernel(const float2* __r
     }
 }
 
-// Output-sensitive form (b2r_volume::d_rows, even R): a surface point needs a voxel with weight != 0, so a count block
-// (256 consecutive voxels) whose (plane, x) rows are all unmarked has nothing to count.  Persistent warps, a warp per count
-// block: one look at the marks, and only for marked rows the four 16-byte loads per lane; the counts are zeroed beforehand.
-// (Skipping inside pc_count2_kernel -- a block per 512 voxels with a barrier around the look -- was SLOWER than streaming
-// the whole cube: 2.66 ms vs 1.88 ms at 1024^3, two million block launches that do nothing.)
-__global__ void __launch_bounds__(256) pc_count_rows_kernel(const float2* __restrict__ tsdfw, const __grid_constant__ PcGeom G,
-                                                            uint32_t* __restrict__ blk_counts, int n_count_blocks,
-                                                            const uint8_t* __restrict__ rows) {
+// Output-sensitive form (b2r_volume::d_rows, even R): a surface point needs q0.x * q1.x < 0, i.e. a NEGATIVE tsdf value at the
+// voxel or at its +x / +y / +z neighbour, so a count block (256 consecutive voxels) none of whose (x, z) rows r has a mark
+// at r, r + 1 (z + 1) or r + R (x + 1) has nothing to count.  pc_cand_kernel, a thread per count block, looks at the marks
+// and appends the candidates to a list (warp-aggregated; order irrelevant, counts are stored by block id);
+// pc_count_list_kernel counts them, persistent warps, a warp per candidate block; the counts are zeroed beforehand.
+// Tried: skipping inside pc_count2_kernel (a block per 512 voxels with a barrier around the look) -- SLOWER than streaming
+// the whole cube, 2.66 vs 1.88 ms at 1024^3; a warp per count block that looks and counts -- 0.77 ms, of which 0.44 the 4.2 M
+// looks; a lane per look and the warp counting its batch's candidates one after the other -- 1.69 ms (the candidates cluster).
+__global__ void __launch_bounds__(256) pc_cand_kernel(const uint8_t* __restrict__ rows, int R, int64_t n, int n_count_blocks,
+                                                      uint32_t* __restrict__ list, unsigned long long* __restrict__ n_cand) {
+    const int b = blockIdx.x * 256 + threadIdx.x, lane = threadIdx.x & 31;
+    bool m = false;
+    if (b < n_count_blocks) {
+        const int64_t t0 = (int64_t)b * PC_THREADS, t1 = min(t0 + PC_THREADS, n) - 1;
+        for (int64_t r = t0 / R; r <= t1 / R; ++r) {     // (r + 1 and r + R stay inside the B2R_PAD_HI planes)
+            const uint8_t* mr = rows + (int64_t)B2R_PAD_LO * R + r;
+            m |= (__ldg(mr) | __ldg(mr + 1) | __ldg(mr + R)) != 0;
+        }
+    }
+    const unsigned live = __ballot_sync(0xffffffffu, m);
+    if (!live) return;
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(n_cand, (unsigned long long)__popc(live));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (m) list[base + __popc(live & ((1u << lane) - 1u))] = (uint32_t)b;
+}
+
+// Points of the voxel pair (x, y, z), (x, y + 1, z) at owned offset t (even: the pair is one 16-byte word, q).  The tests
+// are pc_flags'; the +x and +z neighbours of both voxels come as one 16-byte word each, a's +y neighbour is b.
+__device__ __forceinline__ unsigned pc_pair_count(const float2* __restrict__ own, int R, int64_t t, const float4 q, bool va, bool vb,
+                                                  int x, int y, int z) {
+    if (x < 1 || z < 1 || x > R - 2 || z > R - 2) return 0u;
+    const bool ia = va && y >= 1 && y <= R - 2, ib = vb && y + 1 <= R - 2;
+    if (!(ia | ib)) return 0u;
+    const float4 qx = __ldg(reinterpret_cast<const float4*>(own + t + (int64_t)R * R));
+    const float4 qz = __ldg(reinterpret_cast<const float4*>(own + t + R));
+    const float2 qy = __ldg(own + t + 2);
+    const bool xn = x + 1 < R - 1, zn = z + 1 < R - 1;
+    unsigned c = 0;
+    if (ia) {
+        c += (xn && pc_valid(make_float2(qx.x, qx.y)) && q.x * qx.x < 0.0f) ? 1u : 0u;
+        c += (y + 1 < R - 1 && vb && q.x * q.z < 0.0f) ? 1u : 0u;
+        c += (zn && pc_valid(make_float2(qz.x, qz.y)) && q.x * qz.x < 0.0f) ? 1u : 0u;
+    }
+    if (ib) {
+        c += (xn && pc_valid(make_float2(qx.z, qx.w)) && q.z * qx.z < 0.0f) ? 1u : 0u;
+        c += (y + 2 < R - 1 && pc_valid(qy) && q.z * qy.x < 0.0f) ? 1u : 0u;
+        c += (zn && pc_valid(make_float2(qz.z, qz.w)) && q.z * qz.z < 0.0f) ? 1u : 0u;
+    }
+    return c;
+}
+
+__global__ void __launch_bounds__(256) pc_count_list_kernel(const float2* __restrict__ tsdfw, const __grid_constant__ PcGeom G,
+                                                            uint32_t* __restrict__ blk_counts, const uint32_t* __restrict__ list,
+                                                            const unsigned long long* __restrict__ n_cand) {
     const int R = G.R, lane = threadIdx.x & 31;
     const int64_t n = (int64_t)(G.x_end - G.x_begin) * R * R;
-    const int nwarps = gridDim.x * 8;
-    for (int b = blockIdx.x * 8 + (threadIdx.x >> 5); b < n_count_blocks; b += nwarps) {
-        const int64_t t0 = (int64_t)b * PC_THREADS, t1 = min(t0 + PC_THREADS, n) - 1;
-        bool m = false;
-        for (int64_t r = t0 / R + lane; r <= t1 / R; r += 32) m |= __ldg(&rows[(int64_t)B2R_PAD_LO * R + r]) != 0;
-        if (!__any_sync(0xffffffffu, m)) continue;
+    const float2* own = tsdfw + (int64_t)B2R_PAD_LO * R * R;
+    const unsigned nwarps = gridDim.x * 8, nc = (unsigned)*n_cand;
+    for (unsigned i = blockIdx.x * 8 + (threadIdx.x >> 5); i < nc; i += nwarps) {
+        const unsigned b = list[i];
+        const int64_t t0 = (int64_t)b * PC_THREADS;
+        // the block's first voxel, once per block; a lane's own (x, y, z) only needs divisions when the block spans rows
+        const int64_t r0 = t0 / R;
+        const int yb = (int)(t0 - r0 * R), zb = (int)(r0 % R), xb = G.x_begin + (int)(r0 / R);
         unsigned c = 0;
 #pragma unroll
         for (int k = 0; k < PC_THREADS / 64; ++k) {
-            const int64_t t = t0 + (int64_t)(k * 32 + lane) * 2;
+            const int off = (k * 32 + lane) * 2;
+            const int64_t t = t0 + off;
             if (t < n) {
-                const float4 q = __ldcs(reinterpret_cast<const float4*>(tsdfw + (int64_t)B2R_PAD_LO * R * R + t));
+                const float4 q = __ldcs(reinterpret_cast<const float4*>(own + t));
                 const bool va = pc_valid(make_float2(q.x, q.y)), vb = pc_valid(make_float2(q.z, q.w));
                 if (va | vb) {
-                    const int y = (int)(t % R), z = (int)((t / R) % R), x = G.x_begin + (int)(t / ((int64_t)R * R));
-                    if (va) c += __popc(pc_flags(tsdfw, G, x, y, z));
-                    if (vb) c += __popc(pc_flags(tsdfw, G, x, y + 1, z));
+                    int x = xb, y = yb + off, z = zb;
+                    if (y >= R) { y = (int)(t % R); z = (int)((t / R) % R); x = G.x_begin + (int)(t / ((int64_t)R * R)); }
+                    c += pc_pair_count(own, R, t, q, va, vb, x, y, z);
                 }
             }
         }
@@ -307,8 +357,13 @@ int b2r_extract_points_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_poi
     PcGeom G{R, vol->x_begin, vol->x_end, vol->voxel_length, vol->origin[0], vol->origin[1], vol->origin[2],
              vol->color_type};
     if (vol->d_rows && R % 2 == 0 && (((uintptr_t)vol->d_tsdfw) & 15) == 0) {
+        unsigned long long* n_cand = (unsigned long long*)ctx->small.ptr + SMALL_PC_NCAND;
         B2R_CUDA(cudaMemsetAsync(blk, 0, (size_t)nblocks * sizeof(uint32_t), st));
-        pc_count_rows_kernel<<<ctx->sm_count * 8, 256, 0, st>>>((const float2*)vol->d_tsdfw, G, blk, nblocks, (const uint8_t*)vol->d_rows);
+        B2R_CUDA(cudaMemsetAsync(n_cand, 0, sizeof(unsigned long long), st));
+        // (the candidate list borrows live_list: pc_live_list_kernel overwrites it after the count kernel has read it)
+        pc_cand_kernel<<<cdiv(nblocks, 256), 256, 0, st>>>((const uint8_t*)vol->d_rows, R, n, nblocks, live_list, n_cand);
+        B2R_LAUNCH_CHECK(ctx);
+        pc_count_list_kernel<<<ctx->sm_count * 8, 256, 0, st>>>((const float2*)vol->d_tsdfw, G, blk, live_list, n_cand);
     } else if (R % 2 == 0 && (((uintptr_t)vol->d_tsdfw) & 15) == 0)
         pc_count2_kernel<<<cdiv(nblocks, 2), PC_THREADS, 0, st>>>((const float2*)vol->d_tsdfw, G, blk, nblocks);
     else

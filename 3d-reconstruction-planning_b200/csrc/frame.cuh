@@ -15,6 +15,8 @@ constexpr int SMALL_TOTAL64_B = 129;
 constexpr int SMALL_TOTAL64_C = 130;
 constexpr int SMALL_MC_NLIVE = 131;     // uint64: live virtual blocks of the last b2r_extract_mesh_count
 constexpr int SMALL_PC_NLIVE = 132;     // uint64: live blocks of the last b2r_extract_points_count
+constexpr int SMALL_PC_NCAND = 137;     // uint64: count blocks next to a marked row (b2r_extract_points_count's work list)
+constexpr int SMALL_MC_NCELLS = 136;    // uint64: cells of the last b2r_extract_mesh_count's classify list
 
 constexpr int B2R_MIP_LEVELS = 5;   // max-depth pyramid cells: 8, 16, 32, 64, 128 pixels
 struct MipDesc {

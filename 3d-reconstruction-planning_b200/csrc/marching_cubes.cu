@@ -49,62 +49,89 @@ __device__ __forceinline__ unsigned plane_nibble(const float2* __restrict__ tsdf
     return (a.x < 0.0f ? 1u : 0u) | (b.x < 0.0f ? 2u : 0u) | (c.x < 0.0f ? 4u : 0u) | (d.x < 0.0f ? 8u : 0u);
 }
 
-// grid: (ceil(R/64), ceil(cube x planes / 4), z chunks); block (64, 4): threadIdx.x -> y, threadIdx.y -> x.  A thread
-// marches its (x, y) column along z (the cube index's low / high nibble are the z and z+1 corners, so the carry runs
-// along z whatever the memory order; consecutive z are R voxels apart).
+// Classification runs on CELLS of 4 cube x planes x MC_ZCHUNK cube z steps (all y).
+// Output sensitivity (b2r_volume::d_rows): an active cube has a corner with tsdf < 0, so a cube of row (x, z) can only be
+// active when one of the rows (x, z), (x+1, z), (x, z+1), (x+1, z+1) is marked "may hold a negative value".  A cell none of
+// whose (x..x+4, z0..z1) rows is marked has no active cube: it is never classified and its codes are never written -- the
+// later passes read a cube's code only when row_active says its row holds an active cube (code_at), and such a row's
+// cell was classified.  mc_cells_kernel, a warp per cell, looks at the cell's <= 165 marks and appends the live cells to
+// a list (order irrelevant: every output is addressed by position); without marks every cell is live.
+__global__ void __launch_bounds__(256) mc_cells_kernel(const uint8_t* __restrict__ rows, int R, int x_begin, int xc_lo, int xc_hi,
+                                                       int cells_x, int cells_z, uint32_t* __restrict__ cells,
+                                                       unsigned long long* __restrict__ n_cells) {
+    const int cell = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (cell >= cells_x * cells_z) return;
+    const int cx = cell / cells_z, cz = cell - cx * cells_z;
+    const int xb0 = xc_lo + cx * 4, z0 = cz * MC_ZCHUNK, z1 = min(z0 + MC_ZCHUNK, R - 1);
+    bool m = rows == nullptr;
+    if (rows)
+        for (int t = lane; t < 5 * 33; t += 32) {
+            const int xx = xb0 + t / 33, zz = z0 + t % 33;
+            m |= xx <= xc_hi + 1 && zz <= z1 && __ldg(&rows[(int64_t)(xx - x_begin + B2R_PAD_LO) * R + zz]) != 0;
+        }
+    if (__any_sync(0xffffffffu, m) && lane == 0) cells[atomicAdd(n_cells, 1ull)] = (uint32_t)cell;
+}
+
+// Persistent blocks of (64, 4) threads over (live cell, 64-column y tile) pairs: threadIdx.x -> y, threadIdx.y -> x.  A
+// thread marches its (x, y) column along z (the cube index's low / high nibble are the z and z+1 corners, so the carry
+// runs along z whatever the memory order; consecutive z are R voxels apart).
 __global__ void __launch_bounds__(256) mc_classify_kernel(const float2* __restrict__ tsdfw, uint8_t* __restrict__ code,
                                                           uint8_t* __restrict__ row_active, int R, int x_begin, int xc_lo,
-                                                          int xc_hi, const uint8_t* __restrict__ rows) {
-    const int y = blockIdx.x * 64 + threadIdx.x;
-    const int xb0 = xc_lo + blockIdx.y * 4;
-    const int x = xb0 + threadIdx.y;
-    const int z0 = blockIdx.z * MC_ZCHUNK;
-    const int z1 = min(z0 + MC_ZCHUNK, R - 1);  // cubes z0 .. z1-1 (no cube starts at z = R-1)
-    if (rows) {
-        // Output sensitivity (b2r_volume::d_rows): a cube of row (x, z) can only be active when rows (x, z), (x+1, z),
-        // (x, z+1), (x+1, z+1) all hold weights, and its code is only ever READ next to an active cube (see mc_live), so
-        // a block none of whose (x..x+4, z0..z1) rows is marked has nothing to classify and nothing anyone will read:
-        // it leaves without touching the volume (one ~165-byte look at the marks instead of 64 KB x 33 rows).
-        const int t = threadIdx.y * 64 + threadIdx.x;
-        const int xx = xb0 + t / 33, zz = z0 + t % 33;
-        const bool m = t < 5 * 33 && xx <= xc_hi + 1 && zz <= z1 && rows[(int64_t)(xx - x_begin + B2R_PAD_LO) * R + zz] != 0;
-        if (!__syncthreads_or(m)) return;
-    }
-    if (x > xc_hi || y >= R || z0 >= z1) return;
-    if (y >= R - 1) {  // no cube starts on the last column
-        for (int z = z0; z < z1; ++z) code[vidx(R, x_begin, x, y, z)] = 0;
-        return;
-    }
-    bool v_lo;
-    unsigned n_lo = plane_nibble(tsdfw, R, x_begin, x, y, z0, v_lo);
-    for (int z = z0; z < z1; ++z) {   // (#pragma unroll 4 was measured: 3.18 ms instead of 2.47 ms at 1024^3)
-        bool v_hi;
-        const unsigned n_hi = plane_nibble(tsdfw, R, x_begin, x, y, z + 1, v_hi);
-        const unsigned c = n_lo | (n_hi << 4);
-        const bool active = v_lo && v_hi && c != 0u && c != 255u;
-        code[vidx(R, x_begin, x, y, z)] = active ? (uint8_t)c : (uint8_t)0;
-        if (active) row_active[(int64_t)(x - x_begin + B2R_PAD_LO) * R + z] = 1;   // (x, z) row holds an active cube
-        n_lo = n_hi; v_lo = v_hi;
+                                                          int xc_hi, int cells_z, int tiles_y,
+                                                          const uint32_t* __restrict__ cells,
+                                                          const unsigned long long* __restrict__ n_cells) {
+    const int64_t n_work = (int64_t)*n_cells * tiles_y;
+    for (int64_t wk = blockIdx.x; wk < n_work; wk += gridDim.x) {
+        const int cell = (int)cells[wk / tiles_y], ty = (int)(wk % tiles_y);
+        const int cx = cell / cells_z, cz = cell - cx * cells_z;
+        const int y = ty * 64 + threadIdx.x;
+        const int x = xc_lo + cx * 4 + threadIdx.y;
+        const int z0 = cz * MC_ZCHUNK;
+        const int z1 = min(z0 + MC_ZCHUNK, R - 1);  // cubes z0 .. z1-1 (no cube starts at z = R-1)
+        if (x > xc_hi || y >= R || z0 >= z1) continue;
+        if (y >= R - 1) {  // no cube starts on the last column
+            for (int z = z0; z < z1; ++z) code[vidx(R, x_begin, x, y, z)] = 0;
+            continue;
+        }
+        bool v_lo;
+        unsigned n_lo = plane_nibble(tsdfw, R, x_begin, x, y, z0, v_lo);
+        for (int z = z0; z < z1; ++z) {   // (#pragma unroll 4 was measured: 3.18 ms instead of 2.47 ms at 1024^3)
+            bool v_hi;
+            const unsigned n_hi = plane_nibble(tsdfw, R, x_begin, x, y, z + 1, v_hi);
+            const unsigned c = n_lo | (n_hi << 4);
+            const bool active = v_lo && v_hi && c != 0u && c != 255u;
+            code[vidx(R, x_begin, x, y, z)] = active ? (uint8_t)c : (uint8_t)0;
+            if (active) row_active[(int64_t)(x - x_begin + B2R_PAD_LO) * R + z] = 1;   // (x, z) row holds an active cube
+            n_lo = n_hi; v_lo = v_hi;
+        }
     }
 }
 
-__device__ __forceinline__ unsigned code_at(const uint8_t* __restrict__ code, int R, int x_begin, int xc_lo, int xc_hi,
-                                            int x, int y, int z) {
-    if (z < 0 || z > R - 2 || y < 0 || x < xc_lo || x > xc_hi) return 0u;
+// Code of cube (x, y, z); `on` = row_active of the cube's (x, z) row.  Rows without an active cube may never have been
+// classified (mc_classify_kernel leaves unmarked blocks alone), so their codes are not read: they are 0 by definition.
+__device__ __forceinline__ unsigned code_at(const uint8_t* __restrict__ code, int R, int x_begin, bool on, int x, int y, int z) {
+    if (!on || y < 0) return 0u;
     return (unsigned)__ldg(&code[vidx(R, x_begin, x, y, z)]);
+}
+// row_active of cube row (x, z), 0 outside the cubes this slab classified
+__device__ __forceinline__ bool row_on(const uint8_t* __restrict__ row_active, int R, int x_begin, int xc_lo, int xc_hi, int x, int z) {
+    if (z < 0 || z > R - 2 || x < xc_lo || x > xc_hi) return false;
+    return __ldg(&row_active[(int64_t)(x - x_begin + B2R_PAD_LO) * R + z]) != 0;
 }
 __device__ __forceinline__ unsigned xbit(unsigned c, int a, int b) { return ((c >> a) ^ (c >> b)) & 1u; }
 
 // Owned-edge vertex flags (bit0 +x, bit1 +y, bit2 +z) of voxel (x,y,z).
-__device__ __forceinline__ unsigned edge_flags(const uint8_t* __restrict__ code, int R, int x_begin, int xc_lo,
-                                               int xc_hi, int x, int y, int z, unsigned& own_code) {
-    const unsigned c000 = code_at(code, R, x_begin, xc_lo, xc_hi, x, y, z);
-    const unsigned c0m0 = code_at(code, R, x_begin, xc_lo, xc_hi, x, y - 1, z);
-    const unsigned c00m = code_at(code, R, x_begin, xc_lo, xc_hi, x, y, z - 1);
-    const unsigned c0mm = code_at(code, R, x_begin, xc_lo, xc_hi, x, y - 1, z - 1);
-    const unsigned cm00 = code_at(code, R, x_begin, xc_lo, xc_hi, x - 1, y, z);
-    const unsigned cm0m = code_at(code, R, x_begin, xc_lo, xc_hi, x - 1, y, z - 1);
-    const unsigned cmm0 = code_at(code, R, x_begin, xc_lo, xc_hi, x - 1, y - 1, z);
+__device__ __forceinline__ unsigned edge_flags(const uint8_t* __restrict__ code, const uint8_t* __restrict__ row_active, int R,
+                                               int x_begin, int xc_lo, int xc_hi, int x, int y, int z, unsigned& own_code) {
+    const bool r00 = row_on(row_active, R, x_begin, xc_lo, xc_hi, x, z), r0m = row_on(row_active, R, x_begin, xc_lo, xc_hi, x, z - 1);
+    const bool rm0 = row_on(row_active, R, x_begin, xc_lo, xc_hi, x - 1, z), rmm = row_on(row_active, R, x_begin, xc_lo, xc_hi, x - 1, z - 1);
+    const unsigned c000 = code_at(code, R, x_begin, r00, x, y, z);
+    const unsigned c0m0 = code_at(code, R, x_begin, r00, x, y - 1, z);
+    const unsigned c00m = code_at(code, R, x_begin, r0m, x, y, z - 1);
+    const unsigned c0mm = code_at(code, R, x_begin, r0m, x, y - 1, z - 1);
+    const unsigned cm00 = code_at(code, R, x_begin, rm0, x - 1, y, z);
+    const unsigned cm0m = code_at(code, R, x_begin, rmm, x - 1, y, z - 1);
+    const unsigned cmm0 = code_at(code, R, x_begin, rm0, x - 1, y - 1, z);
     own_code = c000;
     const unsigned fx = xbit(c000, 0, 1) | xbit(c0m0, 3, 2) | xbit(c00m, 4, 5) | xbit(c0mm, 7, 6);
     const unsigned fy = xbit(c000, 0, 3) | xbit(cm00, 1, 2) | xbit(c00m, 4, 7) | xbit(cm0m, 5, 6);
@@ -143,7 +170,8 @@ __global__ void __launch_bounds__(256) mc_live_list_kernel(const uint32_t* __res
 
 // flat thread per owned voxel (memory order).  Writes vert_tab[voxel] = flags << 29 (ids are added by
 // mc_emit_vertices) and per-block totals.
-__global__ void __launch_bounds__(MC_THREADS) mc_count_kernel(const uint8_t* __restrict__ code, int R, int x_begin,
+__global__ void __launch_bounds__(MC_THREADS) mc_count_kernel(const uint8_t* __restrict__ code,
+                                                              const uint8_t* __restrict__ row_active, int R, int x_begin,
                                                               int x_end, int xc_lo, int xc_hi,
                                                               const uint32_t* __restrict__ live_list,
                                                               const unsigned long long* __restrict__ n_live,
@@ -160,7 +188,7 @@ __global__ void __launch_bounds__(MC_THREADS) mc_count_kernel(const uint8_t* __r
         if (t < n) {
             const int y = (int)(t % R), z = (int)((t / R) % R), x = x_begin + (int)(t / ((int64_t)R * R));
             unsigned own;
-            const unsigned f = edge_flags(code, R, x_begin, xc_lo, xc_hi, x, y, z, own);
+            const unsigned f = edge_flags(code, row_active, R, x_begin, xc_lo, xc_hi, x, y, z, own);
             nv = __popc(f);
             nt = d_mc_ntri_table[own];
             vert_tab[vidx(R, x_begin, x, y, z)] = f << 29;
@@ -252,6 +280,7 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_vertices_kernel(const floa
 }
 
 __global__ void __launch_bounds__(MC_THREADS) mc_emit_triangles_kernel(const uint8_t* __restrict__ code,
+                                                                       const uint8_t* __restrict__ row_active,
                                                                        const uint32_t* __restrict__ vert_tab, int R,
                                                                        int x_begin, int x_end, int xc_hi,
                                                                        const uint32_t* __restrict__ live_list,
@@ -268,7 +297,7 @@ __global__ void __launch_bounds__(MC_THREADS) mc_emit_triangles_kernel(const uin
         int x = 0, y = 0, z = 0;
         if (t < n) {
             y = (int)(t % R); z = (int)((t / R) % R); x = x_begin + (int)(t / ((int64_t)R * R));
-            if (x <= xc_hi && z <= R - 2) c = code[vidx(R, x_begin, x, y, z)];
+            if (x <= xc_hi && z <= R - 2 && row_active[(int64_t)(x - x_begin + B2R_PAD_LO) * R + z]) c = code[vidx(R, x_begin, x, y, z)];
         }
         const unsigned nt = d_mc_ntri_table[c];
         uint32_t total;
@@ -337,16 +366,23 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
     uint8_t* row_active = (uint8_t*)ctx->mc_flags.ptr;
     B2R_CUDA(cudaMemsetAsync(row_active, 0, planes * R, st));
     unsigned long long* tot = (unsigned long long*)ctx->small.ptr + SMALL_TOTAL64;
+    if (ctx->mc_live.ensure((size_t)nblocks * 3 * sizeof(uint32_t))) return -102;
     if (xc_hi >= xc_lo) {
-        // (with row marks the code array is not cleared: codes of blocks that leave early are never read)
-        if (!vol->d_rows) B2R_CUDA(cudaMemsetAsync(code, 0, nvox_pad, st));
-        dim3 block(64, 4), grid(cdiv(R, 64), cdiv(xc_hi - xc_lo + 1, 4), cdiv(R - 1, MC_ZCHUNK));
-        mc_classify_kernel<<<grid, block, 0, st>>>((const float2*)vol->d_tsdfw, code, row_active, R, zb, xc_lo, xc_hi,
-                                                   (const uint8_t*)vol->d_rows);
+        // (the code array is not cleared: codes of rows without an active cube are never read)
+        const int cells_x = cdiv(xc_hi - xc_lo + 1, 4), cells_z = cdiv(R - 1, MC_ZCHUNK), tiles_y = cdiv(R, 64);
+        if (ctx->mc_cells.ensure((size_t)cells_x * cells_z * sizeof(uint32_t))) return -102;
+        unsigned long long* n_cells = (unsigned long long*)ctx->small.ptr + SMALL_MC_NCELLS;
+        B2R_CUDA(cudaMemsetAsync(n_cells, 0, sizeof(unsigned long long), st));
+        mc_cells_kernel<<<cdiv(cells_x * cells_z, 8), 256, 0, st>>>((const uint8_t*)vol->d_rows, R, zb, xc_lo, xc_hi, cells_x, cells_z,
+                                                                    (uint32_t*)ctx->mc_cells.ptr, n_cells);
+        B2R_LAUNCH_CHECK(ctx);
+        const int64_t max_work = (int64_t)cells_x * cells_z * tiles_y;
+        const int grid = (int)(max_work < (int64_t)ctx->sm_count * 8 ? max_work : (int64_t)ctx->sm_count * 8);
+        mc_classify_kernel<<<grid, dim3(64, 4), 0, st>>>((const float2*)vol->d_tsdfw, code, row_active, R, zb, xc_lo, xc_hi, cells_z,
+                                                         tiles_y, (const uint32_t*)ctx->mc_cells.ptr, n_cells);
         B2R_LAUNCH_CHECK(ctx);
     }
     // live virtual blocks -> list (device-side count in tot[2]); dead blocks keep zero totals
-    if (ctx->mc_live.ensure((size_t)nblocks * 3 * sizeof(uint32_t))) return -102;
     uint32_t* live = (uint32_t*)ctx->mc_live.ptr;
     uint32_t* live_pos = live + nblocks;
     uint32_t* live_list = live + 2 * (size_t)nblocks;
@@ -356,7 +392,7 @@ int b2r_extract_mesh_count(b2r_ctx* ctx, const b2r_volume* vol, int64_t* n_verti
     mc_live_list_kernel<<<cdiv(nblocks, 256), 256, 0, st>>>(live, live_pos, nblocks, live_list);
     B2R_LAUNCH_CHECK(ctx);
     B2R_CUDA(cudaMemsetAsync(blk_v, 0, (size_t)nblocks * 2 * sizeof(uint32_t), st));
-    mc_count_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, st>>>(code, R, zb, ze, xc_lo, xc_hi, live_list, (unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE, vert_tab, blk_v,
+    mc_count_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, st>>>(code, row_active, R, zb, ze, xc_lo, xc_hi, live_list, (unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE, vert_tab, blk_v,
                                                               blk_t);
     B2R_LAUNCH_CHECK(ctx);
     if (int rc = scan_exclusive_u32(ctx, blk_v, blk_v, nblocks, tot, st)) return rc;
@@ -429,6 +465,7 @@ int b2r_extract_mesh_triangles(b2r_ctx* ctx, const b2r_volume* vol, int32_t* d_t
     const uint32_t* live_list = (const uint32_t*)ctx->mc_live.ptr + 2 * (size_t)nblocks;
     const unsigned long long* n_live = (const unsigned long long*)ctx->small.ptr + SMALL_MC_NLIVE;
     mc_emit_triangles_kernel<<<ctx->sm_count * 8, MC_THREADS, 0, S(stream)>>>((const uint8_t*)ctx->mc_code.ptr,
+                                                                              (const uint8_t*)ctx->mc_flags.ptr,
                                                                               (const uint32_t*)ctx->mc_vert_id.ptr, R,
                                                                               vol->x_begin, vol->x_end, xc_hi, live_list, n_live,
                                                                               blk_t, d_triangles);

@@ -57,9 +57,11 @@ typedef struct b2r_volume {
     void* d_tsdfw;             /* float2 [(x_end-x_begin+PAD_LO+PAD_HI) * R * R] */
     void* d_color;             /* uint32, same count; NULL when color_type == 0 */
     void* d_rows;              /* optional uint8 [(x_end-x_begin+PAD_LO+PAD_HI) * R]: 1 = row (plane x, z) may hold a voxel
-                                * with weight != 0.  Maintained by the library (integrate marks, reset clears, import
-                                * sets all); halo planes travel with the volume's halo planes.  Extraction classifies
-                                * only cube rows next to a marked row; NULL = no information, every row is read. */
+                                * with tsdf < 0 (a surface needs one: an active cube and a surface point both have a
+                                * negative corner).  Maintained by the library (integrate marks the rows of work items
+                                * that integrated a negative sample, reset clears, import sets all); halo planes travel
+                                * with the volume's halo planes.  Extraction reads the volume only next to marked rows;
+                                * NULL = no information, every row is read. */
 } b2r_volume;
 
 /* ---- library / context ------------------------------------------------------------------ */
