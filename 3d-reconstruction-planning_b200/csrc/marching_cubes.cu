@@ -25,7 +25,10 @@
 
 namespace b2r {
 
-constexpr int MC_ZCHUNK = 32;
+#ifndef B2R_MC_ZCHUNK
+#define B2R_MC_ZCHUNK 8         // measured at 1024^3 after the bench orbit: 32 -> 288 us, 16 -> 224 us, 8 -> 200 us (classify)
+#endif
+constexpr int MC_ZCHUNK = B2R_MC_ZCHUNK;
 constexpr int MC_THREADS = 256;
 
 struct McGeom {
@@ -65,8 +68,8 @@ __global__ void __launch_bounds__(256) mc_cells_kernel(const uint8_t* __restrict
     const int xb0 = xc_lo + cx * 4, z0 = cz * MC_ZCHUNK, z1 = min(z0 + MC_ZCHUNK, R - 1);
     bool m = rows == nullptr;
     if (rows)
-        for (int t = lane; t < 5 * 33; t += 32) {
-            const int xx = xb0 + t / 33, zz = z0 + t % 33;
+        for (int t = lane; t < 5 * (MC_ZCHUNK + 1); t += 32) {
+            const int xx = xb0 + t / (MC_ZCHUNK + 1), zz = z0 + t % (MC_ZCHUNK + 1);
             m |= xx <= xc_hi + 1 && zz <= z1 && __ldg(&rows[(int64_t)(xx - x_begin + B2R_PAD_LO) * R + zz]) != 0;
         }
     if (__any_sync(0xffffffffu, m) && lane == 0) cells[atomicAdd(n_cells, 1ull)] = (uint32_t)cell;

@@ -104,3 +104,37 @@ def test_point_cloud_white_noise(o3d, orc):
     b, ob = hp.sort_rows(Pg)
     assert np.abs(a - b).max() < 1e-12
     assert np.abs(N[oa] - Ng[ob]).max() < 1e-9
+
+
+def test_row_marks_cover_negative_rows_and_stale_codes_are_not_read(o3d, orc):
+    """b2r_volume::d_rows: every (x, z) row holding a negative tsdf value is marked (the only rows an active cube or a surface
+    point can need), the free space in front of the surfaces is not, and cells that classification skips keep whatever codes an
+    earlier extraction left in the context's scratch -- here a white-noise volume of the same size, active cubes everywhere --
+    without anyone reading them."""
+    from b200recon import _lib
+    R, L, trunc = 96, 0.384, 0.016
+    rng = np.random.default_rng(5)
+    noise = o3d.pipelines.integration.UniformTSDFVolume(L, R, trunc, o3d.pipelines.integration.TSDFVolumeColorType.RGB8,
+                                                        syn.volume_origin(L))
+    noise.import_arrays(rng.uniform(-1, 1, (R, R, R)).astype(np.float32), np.ones((R, R, R), np.float32),
+                        np.zeros((R, R, R, 3), np.float32))
+    assert len(noise.extract_triangle_mesh().triangles) > 100000
+    assert len(noise.extract_point_cloud().points) > 100000
+    del noise
+    K = hp.small_intrinsic(320, 240)
+    ref, vol = _fused_pair(o3d, orc, R, L, trunc, 6, K)
+    ts, w, _ = vol.export_arrays()
+    marks = vol._rows.cpu().numpy()[_lib.PAD_LO:_lib.PAD_LO + R]          # [x][z]
+    neg = (ts < 0).any(axis=1)                                            # ts is [x][y][z]
+    assert neg.sum() > 100 and marks[neg].all()
+    touched = (w != 0).any(axis=1)
+    assert marks.astype(bool).sum() < 0.6 * touched.sum(), "marks are not output-sensitive"
+    ref_mesh = ref.extract_triangle_mesh()
+    _check_mesh(ref_mesh, vol.extract_triangle_mesh(), L / R)
+    P, N, _ = ref.extract_point_cloud()
+    pcd = vol.extract_point_cloud()
+    Pg, Ng = np.asarray(pcd.points), np.asarray(pcd.normals)
+    assert len(Pg) == len(P)
+    a, oa = hp.sort_rows(P)
+    b, ob = hp.sort_rows(Pg)
+    assert np.abs(a - b).max() <= 1e-4 * (L / R) and np.abs(N[oa] - Ng[ob]).max() < 1e-9
