@@ -65,6 +65,8 @@ SIGNATURES = {
     "b2r_ctx_trace_read": (C.c_int, [c_vp, C.POINTER(C.c_uint64), C.c_int, C.POINTER(C.c_int)]),
     "b2r_depth_to_float": (C.c_int, [c_vp, c_vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, c_vp, c_vp]),
     "b2r_backproject": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, C.POINTER(Intrinsic), c_dp, c_vp, c_vp, c_i64p, c_vp]),
+    "b2r_backproject_static": (C.c_int, [C.c_int, c_vp, c_vp, C.c_int, C.POINTER(Intrinsic), c_dp, c_vp, c_vp, c_vp, c_vp]),
+    "b2r_backproject_static_max_pixels": (C.c_int, [c_i64p]),
     "b2r_integrate": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, c_vp, C.POINTER(Intrinsic), c_dp, c_vp, c_vp]),
     "b2r_integrate_host": (C.c_int, [c_vp, C.POINTER(Volume), c_vp, C.c_int, c_vp, C.POINTER(Intrinsic), c_dp,
                                      C.c_double, C.c_double, c_vp, c_vp]),

@@ -1,6 +1,7 @@
 // Frame-side kernels: depth conversion, frame preparation for integration
 // ({depth, distance-multiplier} float2 image + packed colour, A.3), ordered back-projection (A.2).
 // Reference call sites: stitcher.py:34-46.
+#include <mutex>
 #include "frame.cuh"
 #include "scan.cuh"
 
@@ -206,6 +207,44 @@ __global__ void __launch_bounds__(BP_THREADS) backproject_emit_kernel(const floa
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// b2r_backproject_static: the same back-projection for callers that cannot allocate (CUDA graph capture, serving loops).
+// Its scratch -- the per-block valid counts, turned in place into the blocks' output offsets -- lives in a file-scope
+// device array of fixed size instead of the context's growable cudaMalloc scratch.  Every GPU that loads the library
+// holds these 64 KB until exit; every call on a device shares them (calls that overlap on the GPU race).
+// ---------------------------------------------------------------------------------------------
+constexpr int64_t BP_STATIC_MAX_PIXELS = 4194304;                            // 2^22: 2048 x 2048, 1920 x 1080, 1280 x 720 ...
+constexpr int BP_STATIC_MAX_BLOCKS = (int)(BP_STATIC_MAX_PIXELS / BP_THREADS);   // 16384 counts = 64 KB
+static __device__ __align__(256) uint32_t g_bp_static_scratch[BP_STATIC_MAX_BLOCKS];
+
+// One block turns the <= 16384 block counts into exclusive offsets in place and writes the total (the number of points).
+constexpr int BP_SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(BP_SCAN_THREADS) backproject_static_scan_kernel(uint32_t* __restrict__ counts, int nblocks,
+                                                                                 long long* __restrict__ n_points) {
+    __shared__ uint32_t warp_sums[BP_SCAN_THREADS / 32];
+    constexpr int PER = BP_STATIC_MAX_BLOCKS / BP_SCAN_THREADS;              // 16 consecutive counts per thread
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, base = threadIdx.x * PER;
+    uint32_t v[PER], sum = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) { v[k] = (base + k < nblocks) ? counts[base + k] : 0u; sum += v[k]; }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = warp_sums[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+        warp_sums[lane] = wi - w;                                            // exclusive prefix of the warp totals
+        if (lane == 31) *n_points = (long long)wi;
+    }
+    __syncthreads();
+    uint32_t run = warp_sums[warp] + incl - sum;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) { if (base + k < nblocks) counts[base + k] = run; run += v[k]; }
+}
+
 // 4x4 inverse on the host (double, Gauss-Jordan with partial pivoting).
 void invert4(const double* m, double* out) {
     double a[4][8];
@@ -278,6 +317,64 @@ int b2r_backproject(b2r_ctx* ctx, const float* d_depth, const uint8_t* d_color, 
     B2R_CUDA(cudaMemcpyAsync(ctx->pinned, total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     B2R_CUDA(cudaStreamSynchronize(st));
     *n_points = (int64_t) * (unsigned long long*)ctx->pinned;
+    return 0;
+}
+
+// The device address of g_bp_static_scratch on `device` (which must be current): in host code the array's name is a
+// host-side stand-in, not a device pointer -- a kernel given it would fault or, where the GPU can reach host memory,
+// silently use the wrong memory.  Looked up once per device and cached; no allocation.
+static int bp_static_scratch(int device, uint32_t** out) {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static uint32_t* ptrs[MAX_DEV] = {nullptr};
+    B2R_CHECK(device >= 0 && device < MAX_DEV, -6, "b2r_backproject_static: device %d out of range [0, %d)", device, MAX_DEV);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[device]) {
+        void* p = nullptr;
+        B2R_CUDA(cudaGetSymbolAddress(&p, g_bp_static_scratch));
+        B2R_CHECK(p != nullptr, -100, "b2r_backproject_static: cudaGetSymbolAddress returned a NULL address");
+        ptrs[device] = (uint32_t*)p;
+    }
+    *out = ptrs[device];
+    return 0;
+}
+
+int b2r_backproject_static_max_pixels(int64_t* out) {
+    B2R_CHECK(out, -1, "b2r_backproject_static_max_pixels: NULL argument");
+    *out = BP_STATIC_MAX_PIXELS;
+    return 0;
+}
+
+int b2r_backproject_static(int device, const float* d_depth, const uint8_t* d_color, int nc, const b2r_intrinsic* K,
+                           const double* extrinsic, double* d_points, double* d_colors, int64_t* d_n_points,
+                           void* stream) {
+    B2R_CHECK(d_depth && K && extrinsic && d_points && d_n_points, -1, "b2r_backproject_static: NULL argument");
+    B2R_CHECK(!d_color || nc == 3 || nc == 4, -5, "b2r_backproject_static: colour must have 3 or 4 channels, got %d", nc);
+    B2R_CHECK(K->width >= 0 && K->height >= 0, -6, "b2r_backproject_static: bad image size %d x %d", K->width, K->height);
+    const int64_t n = (int64_t)K->width * K->height;
+    B2R_CHECK(n <= BP_STATIC_MAX_PIXELS, -7,
+              "b2r_backproject_static: %d x %d = %lld pixels exceed the static scratch's maximum of %lld pixels; "
+              "use b2r_backproject (which allocates) for larger images",
+              K->width, K->height, (long long)n, (long long)BP_STATIC_MAX_PIXELS);
+    B2R_CUDA(cudaSetDevice(device));
+    uint32_t* counts = nullptr;
+    if (int rc = bp_static_scratch(device, &counts)) return rc;
+    cudaStream_t st = S(stream);
+    // (nothing in the scratch has to start at zero: the count kernel overwrites the nblocks entries the other two read;
+    //  the previous call's contents beyond them are never looked at)
+    const int nblocks = (int)cdiv(n, BP_THREADS);
+    if (nblocks > 0) backproject_count_kernel<<<nblocks, BP_THREADS, 0, st>>>(d_depth, n, counts);
+    backproject_static_scan_kernel<<<1, BP_SCAN_THREADS, 0, st>>>(counts, nblocks, (long long*)d_n_points);
+    if (nblocks > 0) {
+        BackprojectParams P;
+        double pose[16];
+        invert4(extrinsic, pose);
+        for (int i = 0; i < 12; ++i) P.pose[i] = pose[i];
+        P.fx = K->fx; P.fy = K->fy; P.cx = K->cx; P.cy = K->cy; P.W = K->width; P.nc = nc;
+        backproject_emit_kernel<<<nblocks, BP_THREADS, 0, st>>>(d_depth, d_color, n, P, counts, d_points, d_colors);
+    }
+    const cudaError_t le = cudaGetLastError();
+    B2R_CHECK(le == cudaSuccess, -101, "b2r_backproject_static: kernel launch failed: %s", cudaGetErrorString(le));
     return 0;
 }
 

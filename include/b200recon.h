@@ -112,6 +112,23 @@ int b2r_depth_to_float(b2r_ctx* ctx, const void* d_depth, int dtype, int H, int 
 int b2r_backproject(b2r_ctx* ctx, const float* d_depth, const uint8_t* d_color, int nc, const b2r_intrinsic* K,
                     const double* extrinsic, double* d_points, double* d_colors, int64_t* n_points, void* stream);
 
+/* b2r_backproject without any allocation -- NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, same points/colours in the same order as b2r_backproject; differences:
+ *  - no context: `device` is the CUDA device ordinal (made current by the call);
+ *  - the scratch (per-block counts -> offsets) is a file-scope static __device__ array of 64 KB that every GPU loading
+ *    the library holds until exit; images of more than b2r_backproject_static_max_pixels() = 4 194 304 pixels (2^22) are
+ *    rejected with -7 and a message in b2r_last_error();
+ *  - non-blocking: the point count is written to *d_n_points (int64 in DEVICE memory, caller's) on `stream`;
+ *  - calls no cudaMalloc / cudaFree / allocating routine; the first call on a device looks the array's address up
+ *    (cudaGetSymbolAddress), later calls only launch three kernels.
+ * All calls on a device share the scratch, which keeps the last call's contents (nothing in it needs clearing: each call
+ * overwrites what it reads): calls that OVERLAP on the GPU (different streams, no ordering between them) race. */
+int b2r_backproject_static(int device, const float* d_depth, const uint8_t* d_color, int nc, const b2r_intrinsic* K,
+                           const double* extrinsic, double* d_points, double* d_colors, int64_t* d_n_points,
+                           void* stream);
+int b2r_backproject_static_max_pixels(int64_t* out);
+
 /* ---- TSDF integration (O3D UniformTSDFVolume.integrate(rgbd, intrinsic, extrinsic)) ------ */
 /* d_depth: float32 metres [H,W] (RGBDImage.depth); d_color: uint8 [H,W,3] (RGB8) or float32 [H,W]
  * (Gray32) or NULL (NoColor).  d_updates (optional, uint64 on device) is incremented by the number
