@@ -64,6 +64,7 @@ class Context:
         n = C.c_int(0)
         _lib.check(_lib.load().b2r_ctx_trace_read(self.handle, buf, cap, C.byref(n)))
         a = np.frombuffer(buf, dtype=np.uint64)[: n.value * 16].reshape(n.value, 16).copy()
+        self.trace_raw = a      # col 9: first streaming warp out of work (ns); col 10: sum over warps of (dry time - start)
         return a[:, :8].reshape(n.value, 4, 2), (a[:, 8] >> np.uint64(32)).astype(np.int64), (a[:, 8] & np.uint64(0xffffffff)).astype(np.int64)
 
     def join(self):

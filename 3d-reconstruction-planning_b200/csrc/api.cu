@@ -142,6 +142,7 @@ int b2r_ctx_trace_read(b2r_ctx* c, unsigned long long* out, int cap_calls, int* 
     if (n > 0) B2R_CUDA(cudaMemcpy(out, c->trace.ptr, (size_t)n * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     for (int i = 0; i < n; ++i)
         for (int k = 0; k < 8; k += 2) out[i * 16 + k] = out[i * 16 + k] ? ~out[i * 16 + k] : 0ull;   // stored as max(~start)
+    for (int i = 0; i < n; ++i) out[i * 16 + 9] = out[i * 16 + 9] ? ~out[i * 16 + 9] : 0ull;           // first dry warp, same form
     *n_calls = n;
     return 0;
 }

@@ -65,6 +65,13 @@ for a, b in zip(cuts[:-1], cuts[1:]):
     print("[%4d,%4d) prepare %s  cull %s  plan %s  items %s  step %s  gap %s  plan_end->items_start %s  live tiles %d items %d  host issue %.1f us/call, wall %.1f us/call"
           % (a, b, q(dur[:, 0]), q(dur[:, 3]), q(dur[:, 1]), q(dur[:, 2]), q(step), q(gap), q(slack), np.median(n_live), np.median(n_items),
              1e6 * t_issue / len(frames), 1e6 * t_all / len(frames)))
+    raw = ctx.trace_raw.astype(np.float64)
+    nw = 148 * 5 * 4                      # resident streaming warps (5 blocks per SM, 4 warps per block)
+    dur_i = (raw[:, 5] - raw[:, 4]) / 1000.0
+    first_dry = (raw[:, 5] - raw[:, 9]) / 1000.0          # kernel end - first warp out of work
+    mean_dry = dur_i - raw[:, 10] / nw / 1000.0           # mean over warps of (kernel end - own dry time)
+    print("           streaming tail: first warp dry %s us before the end, mean warp idle %s us = %.1f %% of the kernel"
+          % (q(first_dry), q(mean_dry), 100.0 * np.median(mean_dry / dur_i)))
     if os.environ.get("DUMP"):
         base = tr[0, 0, 0]
         for i in range(min(len(tr), int(os.environ["DUMP"]))):
