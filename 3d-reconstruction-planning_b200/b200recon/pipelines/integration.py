@@ -126,7 +126,7 @@ class UniformTSDFVolume(TSDFVolume):
             raise RuntimeError("[UniformTSDFVolume::Integrate] Unsupported image format. (Gray32 volumes take a float "
                                "colour image through integrate())")
         pinned = isinstance(depth, t.Tensor)
-        if pinned != (isinstance(color, t.Tensor) or color is None):
+        if color is not None and pinned != isinstance(color, t.Tensor):
             raise RuntimeError("integrate_host: depth and colour must both be numpy arrays or both torch CPU tensors")
         if pinned:
             if depth.is_cuda or (color is not None and color.is_cuda):

@@ -161,6 +161,32 @@ def test_integrate_errors(o3d):
     vol.reset()
 
 
+def test_integrate_rejects_frames_of_2_23_pixels_and_recovers(o3d, orc):
+    """The streaming kernel's pixel index lives in a float32 mantissa next to 2^23 (exact below 2^24): frames of 2^23 pixels or
+    more are rejected by the host with a clear error, and the context's frame slot is usable afterwards -- the next, normal
+    frame integrates bit-exactly."""
+    import torch
+    from b200recon import runtime
+    NoColor = o3d.pipelines.integration.TSDFVolumeColorType.NoColor
+    vol = o3d.pipelines.integration.UniformTSDFVolume(0.384, 64, 0.024, NoColor, syn.volume_origin(0.384))
+    big = o3d.camera.PinholeCameraIntrinsic(4096, 2048, 3000.0, 3000.0, 2048.0, 1024.0)       # exactly 2^23 pixels
+    depth = torch.ones((2048, 4096), dtype=torch.float32, device=runtime.ctx(0).tdev)
+    with pytest.raises(RuntimeError, match="2\\^23"):
+        vol.integrate_device(depth, None, big, np.eye(4))
+    del depth
+    K = hp.small_intrinsic(320, 240)
+    frames = hp.make_frames(2, K)
+    ref, vols, n_ref = _run_pair(o3d, orc, 64, 0.384, 0.024, frames, K, color_type=0)
+    _compare(ref, vols, n_ref, 0)
+    # ... and on the volume that saw the error
+    kt = hp.kt(K)
+    intr = o3d.camera.PinholeCameraIntrinsic(K["width"], K["height"], *kt)
+    for d16, rgb, ext in frames:
+        vol.integrate_host(d16, None, intr, ext)
+    ts, w, _ = vol.export_arrays()
+    assert np.array_equal(w, ref.weight()) and np.array_equal(ts.view(np.uint32), ref.tsdf().view(np.uint32))
+
+
 def test_shared_reciprocal_division_is_ieee(o3d):
     """The kernel's float32 divisions (projection, running mean) share a refined reciprocal; on the device they
     must equal the `/` operator bit for bit (2^28 pseudo-random cases incl. near-half-way quotients)."""
